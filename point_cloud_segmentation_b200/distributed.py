@@ -1,0 +1,116 @@
+"""Multi-GPU voxel-map exchange: one process per GPU, frames sharded by rank, voxels owned by spatial hash.
+
+The reference has no multi-process path (single ROS spinner thread).  The scan-level accumulation it
+performs -- the octree built from the concatenation of all frames' labelled points
+(pcs_scan_integration/src/pcs_scan_integration/octomap_mesh_masking.cpp:105-116) -- is a commutative count reduction
+keyed by voxel, so it shards with exactly one exchange step:
+
+  1. every rank integrates its own frames into a LOCAL map (pre-aggregation: tens of points per voxel per frame)
+  2. local voxels are packed as 16-byte records {key48, count0 | count1 << 32}, grouped by owner = mix64(key48) % G
+  3. one all-to-all of the group sizes, one all-to-all of the records (NCCL over NVLink / NVSwitch)
+  4. each rank adds what it received into its OWNED map slice (atomic adds; integers, so arrival order is irrelevant)
+
+For the mesh mask every rank needs the full map: `allgather_owned` gathers the owned slices and merges them.
+torch.distributed is plumbing only (process group, NCCL calls, the exchange buffers); packing and merging are
+kernels of libpcs_b200 reached through the C ABI.  The same class runs on the gloo backend with CPU tensors when the
+maps are given as objects with the small interface below, which is how the host-side logic is tested without GPUs.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+RECORD_BYTES = 16
+
+
+class GpuMapAdapter:
+    """Adapts a capi.VoxelMap (device hash) to the exchange: records live in torch CUDA tensors."""
+
+    def __init__(self, ctx, vmap):
+        self.ctx = ctx
+        self.vmap = vmap
+
+    def size(self) -> int:
+        return self.vmap.size()[0]
+
+    def clear(self):
+        self.vmap.clear()
+
+    def pack_by_owner_into(self, n_owners: int, buf) -> np.ndarray:
+        """buf: torch.int64 tensor with 2 elements per record, on this rank's device."""
+        return self.vmap.pack_by_owner_dev(n_owners, buf.data_ptr(), buf.numel() // 2)
+
+    def merge_records_from(self, buf, n: int):
+        self.vmap.merge_records_dev(buf.data_ptr(), n)
+
+
+class MapExchange:
+    """Owner-partitioned reduction of per-rank voxel maps."""
+
+    def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int, local=None, owned=None, device=None):
+        self.dist = dist
+        self.torch = torch
+        self.world = dist.get_world_size()
+        self.rank = dist.get_rank()
+        if local is None:
+            local = GpuMapAdapter(ctx, vmap)
+            self._owned_map = ctx.create_map(vmap.resolution, capacity_voxels)
+            owned = GpuMapAdapter(ctx, self._owned_map)
+            device = torch.device("cuda", ctx.device)
+        self.local = local
+        self.owned = owned
+        self.device = device
+        self._send = None
+        self._recv = None
+        self.last_sent_records = 0
+        self.last_recv_records = 0
+
+    def _buffer(self, which: str, n_records: int):
+        cur = getattr(self, which)
+        if cur is None or cur.numel() < 2 * n_records:
+            cur = self.torch.empty(2 * max(n_records, 1024) * 5 // 4, dtype=self.torch.int64, device=self.device)
+            setattr(self, which, cur)
+        return cur
+
+    def exchange(self, clear_owned: bool = True):
+        """Route every local voxel record to its owner and merge the received ones into the owned slice."""
+        torch, dist = self.torch, self.dist
+        n_local = self.local.size()
+        send = self._buffer("_send", n_local)
+        counts = np.asarray(self.local.pack_by_owner_into(self.world, send), dtype=np.int64)
+        assert int(counts.sum()) == n_local
+        send_counts = torch.from_numpy(counts.copy()).to(self.device)
+        recv_counts = torch.empty_like(send_counts)
+        dist.all_to_all_single(recv_counts, send_counts)
+        rc = recv_counts.cpu().numpy().astype(np.int64)
+        n_recv = int(rc.sum())
+        recv = self._buffer("_recv", n_recv)
+        dist.all_to_all_single(recv[: 2 * n_recv], send[: 2 * n_local],
+                               output_split_sizes=[int(2 * c) for c in rc],
+                               input_split_sizes=[int(2 * c) for c in counts])
+        if clear_owned:
+            self.owned.clear()
+        self.owned.merge_records_from(recv, n_recv)
+        self.last_sent_records = n_local
+        self.last_recv_records = n_recv
+        return n_recv
+
+    def allgather_owned(self, into):
+        """Merge every rank's owned slice into `into` (same interface) so that each rank holds the whole map."""
+        torch, dist = self.torch, self.dist
+        n_own = self.owned.size()
+        send = self._buffer("_send", n_own)
+        self.owned.pack_by_owner_into(1, send)
+        sizes = torch.zeros(self.world, dtype=torch.int64, device=self.device)
+        mine = torch.tensor([n_own], dtype=torch.int64, device=self.device)
+        dist.all_gather_into_tensor(sizes, mine)
+        sz = sizes.cpu().numpy().astype(np.int64)
+        mx = int(sz.max()) if sz.size else 0
+        recv = self._buffer("_recv", mx * self.world)
+        padded = send[: 2 * mx] if send.numel() >= 2 * mx else torch.cat(
+            [send, torch.zeros(2 * mx - send.numel(), dtype=torch.int64, device=self.device)])
+        dist.all_gather_into_tensor(recv[: 2 * mx * self.world], padded.contiguous())
+        for r in range(self.world):
+            n = int(sz[r])
+            if n:
+                into.merge_records_from(recv[2 * mx * r: 2 * mx * r + 2 * n], n)
+        return int(sz.sum())

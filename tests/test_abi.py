@@ -1,0 +1,77 @@
+"""The C-ABI library loads and exports every symbol include/pcs_b200.h declares (no compute calls: runs on CPU)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def built():
+    from point_cloud_segmentation_b200 import _build
+
+    return _build.build()
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "pcs_b200.h")).read()
+    return sorted(set(re.findall(r"PCS_API\s+[\w\s\*]+?\b(pcs_\w+)\s*\(", text)))
+
+
+def test_header_symbols_all_exported(built):
+    lib = ctypes.CDLL(built)
+    names = declared_symbols()
+    assert len(names) >= 40
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/pcs_b200.h but not exported"
+
+
+def test_binding_table_matches_header(built):
+    from point_cloud_segmentation_b200 import capi
+
+    assert sorted(capi.SIGNATURES) == declared_symbols()
+    capi.load_library()
+
+
+def test_no_torch_or_oracle_in_product():
+    """The product path must not import the oracle (test infrastructure) nor route through torch."""
+    pkg = os.path.join(ROOT, "point_cloud_segmentation_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", src, re.M), f
+                assert "pcs_oracle.h" not in src and "libpcs_oracle" not in src, f
+
+
+def test_pod_layouts():
+    from point_cloud_segmentation_b200 import capi
+
+    assert capi.POINT_DTYPE.itemsize == 32 and capi.POINT_DTYPE.fields["b"][1] == 16  # sizeof(pcl::PointXYZRGB)
+    assert ctypes.sizeof(capi.HsvParams) == 32 and ctypes.sizeof(capi.AnnotateParams) == 48
+
+
+def test_version_and_defaults_without_gpu(built):
+    from point_cloud_segmentation_b200 import capi
+
+    assert capi.load_library().pcs_version() == 100
+    p = capi.hsv_params()
+    assert (p.h_lo, p.h_hi, p.s_lo, p.s_hi, p.v_lo, p.v_hi) == (95, 115, 95, 220, 40, 150)  # hsv_thresholding.h:47-52
+    a = capi.annotate_params()
+    assert (a.lower, a.upper, a.limit_negative) == (0, 255, 0)  # octomap_mesh_masking.h:107-109
+    assert capi.mix64(0) == 0 and capi.mix64(1) != 1
+
+
+def test_fails_loudly_without_cuda(built):
+    """On a box without a GPU the product refuses to run instead of falling back to anything."""
+    from point_cloud_segmentation_b200 import capi
+
+    lib = capi.load_library()
+    h = ctypes.c_void_p()
+    rc = lib.pcs_ctx_create(0, None, ctypes.byref(h))
+    if rc != 0:
+        assert rc == capi.PCS_ERR_CUDA and b"no CPU fallback" in lib.pcs_last_error()
+    else:  # running on the GPU box
+        lib.pcs_ctx_destroy(h)
