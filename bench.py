@@ -21,7 +21,6 @@ import argparse
 import json
 import math
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -60,45 +59,71 @@ def peak_hbm_gbs():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
-
-    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """Samples SM clocks / throttle reasons of one GPU while the timed region runs (NVML, ~1 ms period; nvidia-smi
+    process spawns are far too slow for a region that lasts tens of milliseconds)."""
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.rows = []
+        self.sm, self.reason_bits = [], 0
+        self.sm_max = None
         self._stop = threading.Event()
         self._t = None
+        self._nvml = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(self._physical_index(gpu_index))
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nvml = None
+
+    @staticmethod
+    def _physical_index(i: int) -> int:
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[i])
+            except Exception:
+                return i
+        return i
+
+    def _sample(self):
+        nv = self._nvml
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+        try:
+            self.reason_bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+        except Exception:
+            self.reason_bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.FIELDS}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 6:
-                    self.rows.append(parts)
+                self._sample()
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(0.001)
 
     def __enter__(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
+        if self._nvml is not None:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
         return self
 
     def __exit__(self, *a):
         self._stop.set()
-        self._t.join(timeout=10)
+        if self._t is not None:
+            self._t.join(timeout=10)
 
     def summary(self) -> dict:
-        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        if self._nvml is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "error": "NVML unavailable"}
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                "hw_power_brake_slowdown": 0x80}
+        reasons = [n for n, b in bits.items() if self.reason_bits & b]
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": reasons, "samples": len(self.sm)}
 
 
 def cpu_baseline_sample(O, frames_host, poses, n_frames, w, h, res, threads):
@@ -257,7 +282,7 @@ def main():
     k_avg_ms = float(np.mean(k_ms))
     achieved = BYTES_PER_POINT * n_pts / (k_avg_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": load_ncu_traffic(), "kernel": "annotate_kernel<map,ann,mask>", "kernel_ms": k_avg_ms,
+                "traffic": load_ncu_traffic(n_pts), "kernel": "annotate_kernel<map,ann,mask>", "kernel_ms": k_avg_ms,
                 "algorithmic_bytes_per_launch": BYTES_PER_POINT * n_pts, "peak_source": peak_src}
 
     # ---- end to end through the host-pointer C ABI call (H2D + kernels + D2H inside the timed region) ---------
@@ -308,12 +333,14 @@ def main():
         dist.destroy_process_group()
 
 
-def load_ncu_traffic():
-    """dram bytes per launch of the annotate kernel from the committed ncu capture of this workload, else None."""
+def load_ncu_traffic(n_points):
+    """dram bytes per launch of the annotate kernel: bytes/point of the committed ncu capture (profiles/) scaled to this
+    launch's point count, else None."""
     p = os.path.join(ROOT, "profiles", "annotate_traffic.json")
     try:
         with open(p) as f:
-            return json.load(f).get("dram_bytes_per_launch")
+            j = json.load(f)
+        return int(round(j["dram_bytes_per_launch"] / j["points_per_launch"] * n_points))
     except Exception:
         return None
 
