@@ -150,6 +150,23 @@ PCS_API int pcs_image_to_cloud(pcs_ctx* ctx, const uint8_t* annotation_bgr, cons
  * lower > upper -> PCS_ERR_BAD_ARG (the reference logs and asserts, .cpp:65-69). */
 PCS_API int pcs_color_passthrough(pcs_ctx* ctx, const pcs_point_xyzrgb* in, uint64_t n, int lower, int upper,
                                   int limit_negative, pcs_point_xyzrgb* out, uint64_t* n_out);
+/* No counterpart in the reference.  Same filter as pcs_color_passthrough, for hosts that must not let the library
+ * allocate: a per-frame callback where cudaMalloc / cudaFree would stall every stream on the device, or a GPU shared
+ * with a process that reserved nearly all device memory at start-up, where a late allocation can fail.  The call
+ * allocates nothing (no cudaMalloc / cudaFree, no library scratch growth):
+ *   - in_dev, out_dev (room for n points) and n_out_dev (one uint64_t) are DEVICE pointers owned by the caller; the
+ *     work is enqueued on the context's stream and the count stays on the device;
+ *   - the per-block counts and offsets of the compaction live in a fixed 48.25 KiB array inside the library image,
+ *     which every GPU that loads the library holds until the process exits;
+ *   - n may not exceed PCS_NOALLOC_MAX_POINTS (one 3840x2160 frame fits); more returns PCS_ERR_CAPACITY;
+ *   - all calls on a device share that array and it keeps the previous call's contents (nothing in it needs to start
+ *     at zero); calls whose kernels overlap on the GPU race on it, so keep them ordered;
+ *   - the first call on a device looks up the array's device address once: make that first call before starting any
+ *     stream capture. */
+#define PCS_NOALLOC_MAX_POINTS (1ull << 23)
+PCS_API int pcs_color_passthrough_noalloc_dev(pcs_ctx* ctx, const pcs_point_xyzrgb* in_dev, uint64_t n, int lower,
+                                              int upper, int limit_negative, pcs_point_xyzrgb* out_dev,
+                                              uint64_t* n_out_dev);
 /* Replaces pcl_ros::transformPointCloud as called at pcs_ros/src/octomap_mesh_mask_node.cpp:56-57: `pose` is a
  * row-major float 4x4; x' = ((m00 x + m01 y) + m02 z) + m03 in float without contraction; non-finite points are
  * copied unchanged. */

@@ -21,6 +21,7 @@ POINT_DTYPE = np.dtype(
      ("pad", "<u4", (3,))]
 )
 assert POINT_DTYPE.itemsize == 32
+NOALLOC_MAX_POINTS = 1 << 23  # PCS_NOALLOC_MAX_POINTS
 RECORD_DTYPE = np.dtype([("key48", "<u8"), ("counts", "<u8")])
 
 
@@ -75,6 +76,7 @@ SIGNATURES = {
     "pcs_cloud_to_image": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "pcs_image_to_cloud": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "pcs_color_passthrough": (_i, [_vp, _vp, _u64, _i, _i, _i, _vp, _pu64]),
+    "pcs_color_passthrough_noalloc_dev": (_i, [_vp, _vp, _u64, _i, _i, _i, _vp, _vp]),
     "pcs_transform_cloud": (_i, [_vp, _vp, _vp, _u64, _vp]),
     "pcs_annotate_frames": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, C.POINTER(AnnotateParams), _vp, _vp]),
     "pcs_annotate_frames_dev": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, C.POINTER(AnnotateParams), _vp, _vp]),
@@ -363,6 +365,12 @@ class Context:
         _check(self.lib.pcs_color_passthrough(self.h, _p(cloud), cloud.size, int(lower), int(upper), int(limit_negative),
                                               _p(out), C.byref(n)))
         return out[: int(n.value)].copy()
+
+    def color_passthrough_noalloc_dev(self, in_dev: int, n: int, lower: int, upper: int, limit_negative: bool,
+                                      out_dev: int, n_out_dev: int):
+        """Allocation-free filter on caller-owned device buffers (at most NOALLOC_MAX_POINTS points); asynchronous."""
+        _check(self.lib.pcs_color_passthrough_noalloc_dev(self.h, _p(in_dev), int(n), int(lower), int(upper),
+                                                          int(limit_negative), _p(out_dev), _p(n_out_dev)))
 
     def transform_cloud(self, pose: np.ndarray, cloud: np.ndarray) -> np.ndarray:
         cloud = _c(cloud, POINT_DTYPE)
