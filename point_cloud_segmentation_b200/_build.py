@@ -56,6 +56,24 @@ def _compile(src: str, verbose: bool, extra: list[str]) -> str:
     return obj
 
 
+def build_variant(name: str, defines: list[str]) -> str:
+    """Tuning aid: libpcs_b200 with extra -D flags, written to csrc/build/variants/<name>.so (select it with
+    PCS_B200_LIB=<path>)."""
+    vdir = os.path.join(BUILD_DIR, "variants", name)
+    os.makedirs(vdir, exist_ok=True)
+    objs = []
+    for src in sources():
+        obj = os.path.join(vdir, src[:-3] + ".o")
+        cmd = [nvcc(), *ARCH_FLAGS, *COMMON_FLAGS, *defines]
+        if src in NO_FMAD:
+            cmd.append("-fmad=false")
+        subprocess.run(cmd + ["-c", os.path.join(CSRC, src), "-o", obj], check=True)
+        objs.append(obj)
+    out = os.path.join(BUILD_DIR, "variants", name + ".so")
+    subprocess.run([nvcc(), *ARCH_FLAGS, "-shared", "-o", out, *objs], check=True)
+    return out
+
+
 def build(force: bool = False, verbose: bool = False, extra_flags: list[str] | None = None) -> str:
     """Compile every csrc/*.cu for sm_100a and link libpcs_b200.so.  Returns the library path."""
     os.makedirs(BUILD_DIR, exist_ok=True)

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libpcs_b200.so")
+LIB_PATH = os.environ.get("PCS_B200_LIB") or os.path.join(_PKG, "libpcs_b200.so")  # env override: kernel variants
 
 PCS_OK, PCS_ERR_BAD_ARG, PCS_ERR_CUDA, PCS_ERR_CAPACITY, PCS_ERR_COMM = 0, 1, 2, 3, 4
 RETURN_INSIDE, RETURN_OUTSIDE, RETURN_COLORIZED = 0, 1, 2

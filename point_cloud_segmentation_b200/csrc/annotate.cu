@@ -21,9 +21,22 @@ namespace pcs
 int launch_hsv_mask(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, int height, size_t stride,
                     const pcs_hsv_params* p, uint8_t* mask_dev, size_t mask_stride, int out_channels);
 
-constexpr int kAnnThreads = 256;
-constexpr int kAnnUnroll = 2;
-constexpr int kAnnTile = kAnnThreads * kAnnUnroll;
+#ifndef PCS_ANN_UNROLL
+#define PCS_ANN_UNROLL 2
+#endif
+#ifndef PCS_ANN_ROUNDS
+#define PCS_ANN_ROUNDS 4
+#endif
+#ifndef PCS_ANN_MIN_BLOCKS
+#define PCS_ANN_MIN_BLOCKS 4
+#endif
+#ifndef PCS_ANN_THREADS
+#define PCS_ANN_THREADS 256
+#endif
+constexpr int kAnnThreads = PCS_ANN_THREADS;
+constexpr int kAnnUnroll = PCS_ANN_UNROLL;            // points in flight per thread
+constexpr int kAnnRounds = PCS_ANN_ROUNDS;            // rounds per tile
+constexpr int kAnnTile = kAnnThreads * kAnnUnroll * kAnnRounds;  // 2048 points: one pose / frame lookup per tile
 
 struct AnnotateArgs
 {
@@ -42,94 +55,124 @@ struct AnnotateArgs
   MapView map;
 };
 
+struct Pose
+{
+  float m[12];
+};
+
+// everything that happens to one point once its 32 bytes have arrived
 template <bool HAS_MAP, bool WRITE_ANN, bool WRITE_MASK, bool MASK_IN>
-__global__ void __launch_bounds__(kAnnThreads, 4) annotate_kernel(const AnnotateArgs a)
+__device__ __forceinline__ void annotate_point(const AnnotateArgs& a, const int* __restrict__ s_lut, const Pose& P,
+                                               const bool has_pose, const Point8& p, const unsigned long long idx,
+                                               const bool in_frame)
+{
+  bool det;
+  if (MASK_IN)
+    det = in_frame && a.mask_in[idx] != 0;
+  else
+  {
+    const int b = p.rgba & 0xff, g = (p.rgba >> 8) & 0xff, r = (p.rgba >> 16) & 0xff;
+    det = hsv_in_range(s_lut, b, g, r, a.hsv) != (a.inverted != 0);
+  }
+  const float x = p.x, y = p.y, z = p.z;
+  float wx = x, wy = y, wz = z;
+  if (has_pose && (HAS_MAP || WRITE_ANN))
+  {
+    // non-finite inputs come out non-finite in every component (NaN * 0 = NaN), so no test is needed before
+    wx = xform_row(P.m[0], P.m[1], P.m[2], P.m[3], x, y, z);
+    wy = xform_row(P.m[4], P.m[5], P.m[6], P.m[7], x, y, z);
+    wz = xform_row(P.m[8], P.m[9], P.m[10], P.m[11], x, y, z);
+  }
+  if (in_frame)
+  {
+    if (WRITE_MASK && !MASK_IN)
+      a.mask[idx] = det ? 255 : 0;
+    if (WRITE_ANN)
+    {
+      Point8 o;
+      // pcl::transformPointCloud leaves non-finite points untouched
+      const bool w = a.world_out != 0 && finite3(x, y, z);
+      o.x = w ? wx : x;
+      o.y = w ? wy : y;
+      o.z = w ? wz : z;
+      o.w = 1.0f;                       // pcl::PointXYZRGB() sets data[3] = 1
+      o.rgba = det ? 0x00ffffffu : 0u;  // r = g = b = mask, alpha 0 (utils.h:161-162)
+      o.p0 = o.p1 = o.p2 = 0u;
+      st_point_stream(a.ann + idx, o);
+    }
+  }
+  if (HAS_MAP)
+  {
+    unsigned int kx, ky, kz;
+    bool valid = in_frame && finite3(wx, wy, wz);
+    valid = coord_to_key(a.map.inv_res, wx, kx) && valid;
+    valid = coord_to_key(a.map.inv_res, wy, ky) && valid;
+    valid = coord_to_key(a.map.inv_res, wz, kz) && valid;
+    const unsigned long long key = ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | kx;
+    const bool cls1 = det ? (a.pass_white != 0) : (a.pass_black != 0);
+    map_add_warp(a.map, valid, key, cls1);
+  }
+}
+
+template <bool HAS_MAP, bool WRITE_ANN, bool WRITE_MASK, bool MASK_IN>
+__global__ void __launch_bounds__(kAnnThreads, PCS_ANN_MIN_BLOCKS) annotate_kernel(const AnnotateArgs a)
 {
   __shared__ int s_lut[512];
   if (!MASK_IN)
     load_hsv_lut(s_lut);
   __syncthreads();
+  const bool has_pose = (a.poses != nullptr);
 
   for (unsigned int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
   {
     const unsigned int frame = tile / a.tiles_per_frame;
     const unsigned int t_in_frame = tile - frame * a.tiles_per_frame;
     const unsigned long long frame_base = (unsigned long long)frame * a.pts_per_frame;
-
-    float m[12];
-    const bool has_pose = (a.poses != nullptr);
+    Pose P;
     if (has_pose && (HAS_MAP || WRITE_ANN))
     {
-      const float* P = a.poses + (size_t)frame * 16;
+      const float4* src = reinterpret_cast<const float4*>(a.poses + (size_t)frame * 16);
 #pragma unroll
-      for (int i = 0; i < 12; i++)
-        m[i] = __ldg(P + i);
+      for (int i = 0; i < 3; i++)
+      {
+        const float4 v = __ldg(src + i);
+        P.m[4 * i + 0] = v.x;
+        P.m[4 * i + 1] = v.y;
+        P.m[4 * i + 2] = v.z;
+        P.m[4 * i + 3] = v.w;
+      }
     }
-
-    Point8 p[kAnnUnroll];
-    bool in_frame[kAnnUnroll];
-    unsigned long long idx[kAnnUnroll];
+    // software pipeline over the rounds of the tile: the loads of round r + 1 are in flight while round r is processed.
+    // The round loop is deliberately NOT unrolled: the body (two inlined points with their hash probes) already is a
+    // few hundred instructions and must stay inside the instruction cache.
+    unsigned int local = t_in_frame * kAnnTile + threadIdx.x;
+    Point8 cur[kAnnUnroll], nxt[kAnnUnroll];
 #pragma unroll
     for (int u = 0; u < kAnnUnroll; u++)
+      if (local + u * kAnnThreads < a.pts_per_frame)
+        cur[u] = ld_point_stream(a.cloud + frame_base + local + u * kAnnThreads);
+#pragma unroll 1
+    for (int r = 0; r < kAnnRounds; r++)
     {
-      const unsigned int local = t_in_frame * kAnnTile + u * kAnnThreads + threadIdx.x;
-      in_frame[u] = local < a.pts_per_frame;
-      idx[u] = frame_base + local;
-      if (in_frame[u])
-        p[u] = ld_point_stream(a.cloud + idx[u]);
-    }
-
+      const unsigned int next_local = local + kAnnUnroll * kAnnThreads;
+      if (r + 1 < kAnnRounds)
+      {
 #pragma unroll
-    for (int u = 0; u < kAnnUnroll; u++)
-    {
-      bool det = false;
-      if (in_frame[u])
-      {
-        if (MASK_IN)
-          det = a.mask_in[idx[u]] != 0;
-        else
-        {
-          const int b = p[u].rgba & 0xff, g = (p[u].rgba >> 8) & 0xff, r = (p[u].rgba >> 16) & 0xff;
-          det = hsv_in_range(s_lut, b, g, r, a.hsv) != (a.inverted != 0);
-        }
+        for (int u = 0; u < kAnnUnroll; u++)
+          if (next_local + u * kAnnThreads < a.pts_per_frame)
+            nxt[u] = ld_point_stream(a.cloud + frame_base + next_local + u * kAnnThreads);
       }
-      const float x = p[u].x, y = p[u].y, z = p[u].z;
-      const bool fin = in_frame[u] && finite3(x, y, z);
-      float wx = x, wy = y, wz = z;
-      if (has_pose && fin && (HAS_MAP || (WRITE_ANN && a.world_out)))
+#pragma unroll
+      for (int u = 0; u < kAnnUnroll; u++)
       {
-        wx = xform_row(m[0], m[1], m[2], m[3], x, y, z);
-        wy = xform_row(m[4], m[5], m[6], m[7], x, y, z);
-        wz = xform_row(m[8], m[9], m[10], m[11], x, y, z);
+        const unsigned int l = local + u * kAnnThreads;
+        annotate_point<HAS_MAP, WRITE_ANN, WRITE_MASK, MASK_IN>(a, s_lut, P, has_pose, cur[u], frame_base + l,
+                                                                l < a.pts_per_frame);
       }
-      if (in_frame[u])
-      {
-        if (WRITE_MASK && !MASK_IN)
-          a.mask[idx[u]] = det ? 255 : 0;
-        if (WRITE_ANN)
-        {
-          Point8 o;
-          const bool w = a.world_out != 0;
-          o.x = w ? wx : x;
-          o.y = w ? wy : y;
-          o.z = w ? wz : z;
-          o.w = 1.0f;                          // pcl::PointXYZRGB() sets data[3] = 1
-          o.rgba = det ? 0x00ffffffu : 0u;     // r=g=b=mask, alpha 0 (utils.h:161-162)
-          o.p0 = o.p1 = o.p2 = 0u;
-          st_point_stream(a.ann + idx[u], o);
-        }
-      }
-      if (HAS_MAP)
-      {
-        unsigned int kx, ky, kz;
-        bool valid = fin;
-        valid = coord_to_key(a.map.inv_res, wx, kx) && valid;
-        valid = coord_to_key(a.map.inv_res, wy, ky) && valid;
-        valid = coord_to_key(a.map.inv_res, wz, kz) && valid;
-        const unsigned long long key = ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | kx;
-        const bool cls1 = det ? (a.pass_white != 0) : (a.pass_black != 0);
-        map_add_warp(a.map, valid, key, cls1);
-      }
+#pragma unroll
+      for (int u = 0; u < kAnnUnroll; u++)
+        cur[u] = nxt[u];
+      local = next_local;
     }
   }
 }
@@ -157,15 +200,15 @@ __global__ void __launch_bounds__(256, 4) integrate_kernel(const Point8* __restr
     p.rgba = 0;
     if (in)
       p = ld_point_stream(pts + i);
-    bool valid = in && finite3(p.x, p.y, p.z);
     float wx = p.x, wy = p.y, wz = p.z;
-    if (has_pose && valid)
+    if (has_pose)
     {
       wx = xform_row(m[0], m[1], m[2], m[3], p.x, p.y, p.z);
       wy = xform_row(m[4], m[5], m[6], m[7], p.x, p.y, p.z);
       wz = xform_row(m[8], m[9], m[10], m[11], p.x, p.y, p.z);
     }
     unsigned int kx, ky, kz;
+    bool valid = in && finite3(wx, wy, wz);  // a non-finite input stays non-finite through the transform
     valid = coord_to_key(map.inv_res, wx, kx) && valid;
     valid = coord_to_key(map.inv_res, wy, ky) && valid;
     valid = coord_to_key(map.inv_res, wz, kz) && valid;
@@ -280,7 +323,7 @@ static int launch_annotate(pcs_ctx* ctx, pcs_map* map, const Point8* clouds, uns
   else
     a.map = MapView{ nullptr, 0, nullptr, nullptr, 0.0 };
 
-  const unsigned int max_blocks = (unsigned int)ctx->sm_count * 8u;  // 8 x 256 threads = one full SM of warps
+  const unsigned int max_blocks = (unsigned int)ctx->sm_count * (unsigned int)PCS_ANN_MIN_BLOCKS;  // one resident wave
   const unsigned int grid = a.n_tiles < max_blocks ? a.n_tiles : max_blocks;
   if (grid == 0)
     return PCS_OK;
@@ -361,6 +404,7 @@ int pcs_annotate_frames_dev(pcs_ctx* ctx, pcs_map* map, const pcs_point_xyzrgb* 
   PCS_CHECK_ARG(params->lower <= params->upper, "colorPassthrough: lower limit greater than upper limit");
   PCS_CHECK_ARG(((uintptr_t)clouds_dev & 31u) == 0 && ((uintptr_t)annotated_out_dev & 31u) == 0,
                 "point buffers must be 32-byte aligned");
+  PCS_CHECK_ARG(((uintptr_t)poses_dev & 15u) == 0, "poses must be 16-byte aligned");
   if (n_frames == 0)
     return PCS_OK;
   return annotate_dev(ctx, map, clouds_dev, n_frames, width, height, poses_dev, params, annotated_out_dev, mask_out_dev);

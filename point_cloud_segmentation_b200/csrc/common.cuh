@@ -125,30 +125,55 @@ __device__ __forceinline__ Point8 ld_point_stream(const void* p)
 
 __device__ __forceinline__ void st_point_stream(void* p, const Point8& v)
 {
+#ifdef PCS_ST_EVICT_FIRST
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w), "r"(v.rgba), "r"(v.p0), "r"(v.p1), "r"(v.p2)
+               : "memory");
+#else
   asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z),
                "f"(v.w), "r"(v.rgba), "r"(v.p0), "r"(v.p1), "r"(v.p2)
                : "memory");
+#endif
 }
 
-// octomap coordToKeyChecked (see oracle/octree.c orc_coord_to_key): explicit range test instead of the UB cast
+// octomap coordToKeyChecked (see oracle/octree.c orc_coord_to_key): k = floor(inv_res * coord) + 32768, valid iff
+// 0 <= k < 65536.  F2I.FLOOR saturates (+-inf and huge values land on INT_MIN / INT_MAX, far outside the range), NaN
+// converts to 0 and must be excluded by the caller's finiteness test on `coord`.
 __device__ __forceinline__ bool coord_to_key(double inv_res, float coord, unsigned int& key)
 {
-  const double s = floor(__dmul_rn(inv_res, (double)coord));
-  const bool ok = (s >= -32768.0) && (s < 32768.0);
-  key = ok ? (unsigned int)((int)s + 32768) : 0u;
-  return ok;
+  const int k = __double2int_rd(__dmul_rn(inv_res, (double)coord));
+  key = (unsigned int)k + 32768u;
+  return key < 65536u;
+}
+
+// table slot of a voxel: classic 3-prime spatial hash of the three 16-bit keys (the owner hash of the multi-GPU
+// exchange is mix64, a different function, so ownership and slot position are independent)
+__device__ __forceinline__ unsigned int slot_hash(unsigned long long key48)
+{
+  const unsigned int kx = (unsigned int)(key48 & 0xffffull), ky = (unsigned int)((key48 >> 16) & 0xffffull),
+                     kz = (unsigned int)((key48 >> 32) & 0xffffull);
+  unsigned int h = (kx * 73856093u) ^ (ky * 19349663u) ^ (kz * 83492791u);
+  return h ^ (h >> 15);
+}
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p)
+{
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
 }
 
 // add (count0 | count1 << 32) to the voxel `key48`, inserting it if needed.  Linear probing, load-before-CAS.
 __device__ __forceinline__ void map_add(const MapView& m, unsigned long long key48, unsigned long long add)
 {
   const unsigned long long want = key48 | kValidBit;
-  unsigned long long slot = mix64(key48) & m.mask;
+  unsigned long long slot = slot_hash(key48) & m.mask;
   // the probe cap keeps a (mis-sized) full table from turning every insert into a scan of the whole table
-  for (unsigned long long probe = 0; probe <= m.mask && probe < 65536ull; ++probe)
+#pragma unroll 1
+  for (unsigned int probe = 0; probe < 65536u; ++probe)
   {
     Slot* s = m.slots + slot;
-    unsigned long long k = *reinterpret_cast<volatile unsigned long long*>(&s->key);
+    unsigned long long k = ld_relaxed_u64(&s->key);
     if (k == 0ull)
     {
       k = atomicCAS(&s->key, 0ull, want);

@@ -121,7 +121,7 @@ __device__ bool key_range(double tmin, double tmax, double res, double inv, int&
 __device__ __forceinline__ bool map_occupied(const MapView& m, unsigned long long key48)
 {
   const unsigned long long want = key48 | kValidBit;
-  unsigned long long slot = mix64(key48) & m.mask;
+  unsigned long long slot = slot_hash(key48) & m.mask;
   for (unsigned long long probe = 0; probe <= m.mask; ++probe)
   {
     const ulonglong2 s = __ldg(reinterpret_cast<const ulonglong2*>(m.slots + slot));
