@@ -35,7 +35,7 @@ BYTES_PER_POINT = 65  # 32 B cloud in + 32 B annotated cloud out + 1 B mask out 
 
 WORKLOADS = {
     # name: (frames per GPU, width, height, resolution, map capacity in voxels)
-    "scan300_1280x720_5mm": (300, 1280, 720, 0.005, 1 << 21),
+    "scan300_1280x720_5mm": (300, 1280, 720, 0.005, 1 << 20),
     "frame1_640x480_1cm": (1, 640, 480, 0.01, 1 << 18),
     "scan16_3840x2160_2mm": (16, 3840, 2160, 0.002, 1 << 23),
 }
@@ -178,6 +178,8 @@ def main():
     ap.add_argument("--frames", type=int, default=0, help="override frames per GPU (debug)")
     ap.add_argument("--ref-frames", type=int, default=32, help="frames per step of the CPU reference arm")
     ap.add_argument("--cpu-frames", type=int, default=200, help="frames of the cpu_baseline sample")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="multi-GPU map exchange: one kernel over NVLink peer memory, or NCCL all-to-all of records")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mesh", action="store_true")
@@ -225,10 +227,23 @@ def main():
     ctx.sync()
 
     exch = None
+    exchange_kind = None
     if world > 1:
-        from point_cloud_segmentation_b200.distributed import MapExchange
+        from point_cloud_segmentation_b200.distributed import MapExchange, PeerMapExchange
 
-        exch = MapExchange(ctx, vmap, dist, torch, cap)
+        exchange_kind = args.exchange
+        if exchange_kind == "peer":
+            try:
+                exch = PeerMapExchange(ctx, vmap, dist, torch, cap)
+            except Exception as e:  # CUDA IPC unavailable on this box: the NCCL-record form gives the same result
+                print(f"[rank {rank}] peer-memory exchange unavailable ({e}); using NCCL records", file=sys.stderr)
+                exchange_kind = "nccl"
+            ok = torch.tensor([1 if exchange_kind == "peer" else 0], device="cuda")
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                exchange_kind = "nccl"
+        if exchange_kind == "nccl":
+            exch = MapExchange(ctx, vmap, dist, torch, cap)
 
     ev = [ctx.event() for _ in range(4)]
 
@@ -317,8 +332,9 @@ def main():
             "config": {"workload": args.workload, "frames_per_gpu": frames_per_gpu, "width": w, "height": h,
                        "voxel_resolution_m": res, "label_filter": "lower=255 upper=255",
                        "outputs": "annotated cloud + mask + voxel map", "l2": "inputs larger than L2 (no flush needed)",
-                       "partition": "frames sharded by rank, voxel owner = mix64(key48) % n_gpus, NCCL all-to-all"
-                       if world > 1 else "single GPU"},
+                       "partition": ("frames sharded by rank, voxel owner = mix64(key48) % n_gpus, exchange = " +
+                                     ("one push kernel over NVLink peer memory (CUDA IPC)" if exchange_kind == "peer"
+                                      else "NCCL all-to-all of 16-byte records")) if world > 1 else "single GPU"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks.summary(), "map": {"voxels": n_vox, "occupied": n_occ},
         }

@@ -224,6 +224,17 @@ PCS_API int pcs_map_pack_by_owner_dev(pcs_ctx* ctx, pcs_map* map, int n_owners, 
                                       uint64_t cap_records, uint64_t* owner_counts);
 PCS_API int pcs_map_merge_records_dev(pcs_ctx* ctx, pcs_map* map, const void* records_dev, uint64_t n);
 PCS_API uint64_t pcs_mix64(uint64_t key48);
+/* Peer-memory form of the exchange (one process per GPU, NVLink / NVSwitch): each rank exports its OWNED map with
+ * pcs_map_ipc_export (a 128-byte CUDA IPC handle pair that the host exchanges by any means), opens every peer's
+ * handle with pcs_map_ipc_open (same resolution / capacity as at creation; destroy with pcs_map_destroy), and then one
+ * kernel, pcs_map_push_to_owners_dev, adds every voxel of the LOCAL map directly into owners[mix64(key48) % n_owners]
+ * with system-scope atomics -- no packing, no staging buffers, no collective for the data.  The host must put a
+ * barrier across ranks before the push (owned maps cleared everywhere) and after it (all pushes landed).
+ * Owner maps may equally be ordinary maps of this process (single-GPU use and tests). */
+PCS_API int pcs_map_ipc_export(pcs_ctx* ctx, pcs_map* map, void* handle128);
+PCS_API int pcs_map_ipc_open(pcs_ctx* ctx, const void* handle128, double resolution, uint64_t capacity_voxels,
+                             pcs_map** peer_map);
+PCS_API int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* owners, int n_owners);
 
 /* ---- stage 4: mesh mask -------------------------------------------------------------------------------------------- */
 /* Replaces OctomapMeshMask::maskMesh(mask_type) (octomap_mesh_masking.h:131, octomap_mesh_masking.cpp:118-283) against

@@ -91,6 +91,9 @@ SIGNATURES = {
     "pcs_map_pack_by_owner_dev": (_i, [_vp, _vp, _i, _vp, _u64, _vp]),
     "pcs_map_merge_records_dev": (_i, [_vp, _vp, _vp, _u64]),
     "pcs_mix64": (_u64, [_u64]),
+    "pcs_map_ipc_export": (_i, [_vp, _vp, _vp]),
+    "pcs_map_ipc_open": (_i, [_vp, _vp, _dbl, _u64, _pp]),
+    "pcs_map_push_to_owners_dev": (_i, [_vp, _vp, _pp, _i]),
     "pcs_mesh_mask": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _i, _u64, _vp, _vp, _vp, _vp, _pu64, _pu64]),
     "pcs_mesh_contacts_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _vp]),
     "pcs_synth_frames_dev": (_i, [_vp, _u64, _i, _i, _i, _i, _vp, _vp]),
@@ -249,6 +252,26 @@ class VoxelMap:
         _check(self.ctx.lib.pcs_map_pack_by_owner_dev(self.ctx.h, self.h, int(n_owners), _p(records_dev),
                                                       int(cap_records), _p(counts)))
         return counts
+
+    def ipc_export(self) -> bytes:
+        """128-byte CUDA IPC handle pair of this map, to be opened by peer processes with VoxelMap.ipc_open."""
+        buf = (C.c_uint8 * 128)()
+        _check(self.ctx.lib.pcs_map_ipc_export(self.ctx.h, self.h, buf))
+        return bytes(buf)
+
+    @classmethod
+    def ipc_open(cls, ctx: "Context", handle: bytes, resolution: float, capacity_voxels: int) -> "VoxelMap":
+        self = cls.__new__(cls)
+        self.ctx, self.resolution = ctx, float(resolution)
+        h = C.c_void_p()
+        buf = (C.c_uint8 * 128).from_buffer_copy(handle)
+        _check(ctx.lib.pcs_map_ipc_open(ctx.h, buf, self.resolution, int(capacity_voxels), C.byref(h)))
+        self.h = h
+        return self
+
+    def push_to_owners_dev(self, owners: "list[VoxelMap]"):
+        arr = (C.c_void_p * len(owners))(*[o.h for o in owners])
+        _check(self.ctx.lib.pcs_map_push_to_owners_dev(self.ctx.h, self.h, arr, len(owners)))
 
     def merge_records_dev(self, records_dev: int, n: int):
         _check(self.ctx.lib.pcs_map_merge_records_dev(self.ctx.h, self.h, _p(records_dev), int(n)))

@@ -67,6 +67,7 @@ struct pcs_map
   uint64_t capacity_voxels;
   uint64_t n_slots;
   unsigned int* d_counters;  // [0] n_used, [1] overflow, [2..] scratch counters
+  bool is_peer;              // memory belongs to another process (opened through CUDA IPC)
 };
 
 struct pcs_ctx

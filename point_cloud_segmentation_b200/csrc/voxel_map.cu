@@ -8,6 +8,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <math.h>
+#include <string.h>
 #include <new>
 
 #include "common.cuh"
@@ -166,6 +167,52 @@ __global__ void owner_scatter_kernel(MapView m, unsigned int n_owners, const uns
   }
 }
 
+// ---- peer-memory exchange: every used slot of the local table is added straight into its owner's table ----------------
+// The owner tables may live on other GPUs (CUDA IPC mappings reached over NVLink), so the insert uses system-scope
+// atomics: a 64-bit CAS claims the slot at the owner's L2, a 64-bit add merges the two counters.
+struct OwnerViews
+{
+  MapView v[16];
+};
+
+__device__ __forceinline__ void map_add_system(const MapView& m, unsigned long long key48, unsigned long long add)
+{
+  const unsigned long long want = key48 | kValidBit;
+  unsigned long long slot = slot_hash(key48) & m.mask;
+#pragma unroll 1
+  for (unsigned int probe = 0; probe < 65536u; ++probe)
+  {
+    Slot* s = m.slots + slot;
+    unsigned long long k = atomicCAS_system(&s->key, 0ull, want);  // one round trip: claims or reads the key
+    if (k == 0ull)
+    {
+      atomicAdd_system(m.n_used, 1u);
+      k = want;
+    }
+    if (k == want)
+    {
+      atomicAdd_system(&s->counts, add);
+      return;
+    }
+    slot = (slot + 1) & m.mask;
+  }
+  *m.overflow = 1u;
+}
+
+__global__ void map_push_to_owners_kernel(MapView local, OwnerViews owners, unsigned int n_owners)
+{
+  const unsigned long long n_slots = local.mask + 1;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots;
+       i += (unsigned long long)gridDim.x * blockDim.x)
+  {
+    const Slot s = local.slots[i];
+    if (!s.key)
+      continue;
+    const unsigned long long k = s.key & ~kValidBit;
+    map_add_system(owners.v[mix64(k) % n_owners], k, s.counts);
+  }
+}
+
 static unsigned int table_grid(pcs_ctx* ctx, unsigned long long n)
 {
   unsigned long long b = (n + 255) / 256;
@@ -219,6 +266,7 @@ int pcs_map_create(pcs_ctx* ctx, double resolution, uint64_t capacity_voxels, pc
   m->resolution = resolution;
   m->capacity_voxels = capacity_voxels;
   m->n_slots = n_slots;
+  m->is_peer = false;
   m->d_counters = nullptr;
   m->view.slots = nullptr;
   cudaError_t e = cudaMalloc(&m->view.slots, n_slots * sizeof(Slot));
@@ -245,8 +293,16 @@ int pcs_map_destroy(pcs_ctx* ctx, pcs_map* map)
     return PCS_OK;
   PCS_TRY(ctx_bind(ctx));
   PCS_CUDA(cudaStreamSynchronize(ctx->stream));
-  cudaFree(map->view.slots);
-  cudaFree(map->d_counters);
+  if (map->is_peer)
+  {
+    cudaIpcCloseMemHandle(map->view.slots);
+    cudaIpcCloseMemHandle(map->d_counters);
+  }
+  else
+  {
+    cudaFree(map->view.slots);
+    cudaFree(map->d_counters);
+  }
   delete map;
   return PCS_OK;
 }
@@ -380,6 +436,72 @@ int pcs_map_merge(pcs_ctx* ctx, pcs_map* map, const uint64_t* key48, const uint3
   PCS_CUDA(cudaStreamSynchronize(ctx->stream));
   ctx->stats.bytes_h2d += n * 16;
   return PCS_OK;
+}
+
+int pcs_map_ipc_export(pcs_ctx* ctx, pcs_map* map, void* handle128)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(map && handle128, "NULL argument");
+  PCS_CHECK_ARG(!map->is_peer, "cannot re-export a peer map");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  cudaIpcMemHandle_t h[2];
+  PCS_CUDA(cudaIpcGetMemHandle(&h[0], map->view.slots));
+  PCS_CUDA(cudaIpcGetMemHandle(&h[1], map->d_counters));
+  memcpy(handle128, h, sizeof(h));
+  return PCS_OK;
+}
+
+int pcs_map_ipc_open(pcs_ctx* ctx, const void* handle128, double resolution, uint64_t capacity_voxels, pcs_map** out)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(handle128 && out, "NULL argument");
+  *out = nullptr;
+  PCS_CHECK_ARG(resolution > 0.0 && capacity_voxels > 0 && capacity_voxels <= (1ull << 31), "bad map geometry");
+  uint64_t n_slots = 1024;
+  while (n_slots < 2 * capacity_voxels)  // must mirror pcs_map_create
+    n_slots <<= 1;
+  cudaIpcMemHandle_t h[2];
+  memcpy(h, handle128, sizeof(h));
+  void *slots = nullptr, *counters = nullptr;
+  PCS_CUDA(cudaIpcOpenMemHandle(&slots, h[0], cudaIpcMemLazyEnablePeerAccess));
+  cudaError_t e = cudaIpcOpenMemHandle(&counters, h[1], cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess)
+  {
+    cudaIpcCloseMemHandle(slots);
+    return cuda_fail(e, "cudaIpcOpenMemHandle(counters)", __FILE__, __LINE__);
+  }
+  pcs_map* m = new (std::nothrow) pcs_map();
+  PCS_CHECK_ARG(m != nullptr, "out of host memory");
+  m->resolution = resolution;
+  m->capacity_voxels = capacity_voxels;
+  m->n_slots = n_slots;
+  m->is_peer = true;
+  m->d_counters = (unsigned int*)counters;
+  m->view.slots = (Slot*)slots;
+  m->view.mask = n_slots - 1;
+  m->view.n_used = m->d_counters;
+  m->view.overflow = m->d_counters + 1;
+  m->view.inv_res = 1.0 / resolution;
+  *out = m;
+  return PCS_OK;
+}
+
+int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* owners, int n_owners)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(local && owners, "NULL argument");
+  PCS_CHECK_ARG(n_owners >= 1 && n_owners <= 16, "n_owners must be in [1, 16]");
+  OwnerViews ov;
+  for (int o = 0; o < n_owners; o++)
+  {
+    PCS_CHECK_ARG(owners[o] != nullptr, "owner map is NULL");
+    PCS_CHECK_ARG(owners[o] != local, "the local map cannot be one of the owners");
+    PCS_CHECK_ARG(owners[o]->resolution == local->resolution, "owner map resolution differs");
+    ov.v[o] = owners[o]->view;
+  }
+  map_push_to_owners_kernel<<<table_grid(ctx, local->n_slots), 256, 0, ctx->stream>>>(local->view, ov, (unsigned int)n_owners);
+  count_launch(ctx);
+  return check_launch("map_push_to_owners_kernel");
 }
 
 int pcs_map_pack_by_owner_dev(pcs_ctx* ctx, pcs_map* map, int n_owners, void* records_dev, uint64_t cap_records,

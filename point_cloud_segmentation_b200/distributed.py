@@ -10,6 +10,11 @@ keyed by voxel, so it shards with exactly one exchange step:
   3. one all-to-all of the group sizes, one all-to-all of the records (NCCL over NVLink / NVSwitch)
   4. each rank adds what it received into its OWNED map slice (atomic adds; integers, so arrival order is irrelevant)
 
+`PeerMapExchange` is the NVLink-native form of steps 2-4: the owned maps are mapped into every process through CUDA
+IPC and ONE kernel (pcs_map_push_to_owners_dev) adds each local voxel straight into its owner's table with
+system-scope atomics over NVLink -- no packing, no staging buffers, no data collective; NCCL only provides the two
+tiny barriers around the push.
+
 For the mesh mask every rank needs the full map: `allgather_owned` gathers the owned slices and merges them.
 torch.distributed is plumbing only (process group, NCCL calls, the exchange buffers); packing and merging are
 kernels of libpcs_b200 reached through the C ABI.  The same class runs on the gloo backend with CPU tensors when the
@@ -114,3 +119,57 @@ class MapExchange:
             if n:
                 into.merge_records_from(recv[2 * mx * r: 2 * mx * r + 2 * n], n)
         return int(sz.sum())
+
+
+class PeerMapExchange:
+    """Owner-partitioned reduction through peer memory: local voxels are pushed into the owners' tables by one kernel.
+
+    Set-up (once): every rank exports the CUDA IPC handles of its owned map, the handles are all-gathered, and each
+    rank opens its peers' tables.  exchange(): clear the owned slice, barrier (everyone has cleared), push kernel,
+    barrier (every push has landed).  The barriers are 4-byte NCCL all-reduces enqueued on the same stream, so the host
+    never blocks."""
+
+    def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int):
+        from . import capi
+
+        self.ctx, self.local, self.dist, self.torch = ctx, vmap, dist, torch
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.device = torch.device("cuda", ctx.device)
+        self.owned_map = ctx.create_map(vmap.resolution, capacity_voxels)
+        ctx.sync()
+        mine = torch.tensor(list(self.owned_map.ipc_export()), dtype=torch.uint8, device=self.device)
+        allh = torch.empty(self.world * 128, dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(allh, mine)
+        allh = allh.cpu().numpy().tobytes()
+        self.owners = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.owners.append(self.owned_map)
+            else:
+                self.owners.append(capi.VoxelMap.ipc_open(ctx, allh[128 * r:128 * (r + 1)], vmap.resolution, capacity_voxels))
+        self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+        dist.barrier()
+
+    @property
+    def owned(self):
+        return GpuMapAdapter(self.ctx, self.owned_map)
+
+    def _barrier(self):
+        self.dist.all_reduce(self._token)  # stream-ordered, no host synchronisation
+
+    def exchange(self, clear_owned: bool = True):
+        if clear_owned:
+            self.owned_map.clear()
+        self._barrier()
+        self.local.push_to_owners_dev(self.owners)
+        self._barrier()
+
+    def close(self):
+        self.ctx.sync()
+        self.dist.barrier()
+        for r, m in enumerate(self.owners):
+            if r != self.rank:
+                m.destroy()
+        self.owners = []
+        self.dist.barrier()
+        self.owned_map.destroy()

@@ -1,0 +1,59 @@
+"""Worker of tests/test_gpu_multigpu.py: run under torch.distributed.run with one process per GPU.
+
+Every rank integrates its own frames, then the owner-partitioned exchange runs twice -- through NCCL records
+(distributed.MapExchange) and through peer memory (distributed.PeerMapExchange) -- and both owned slices are written
+to OUT_DIR for the parent test to compare with the single-GPU answer."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import bench  # noqa: E402
+import point_cloud_segmentation_b200 as pcs  # noqa: E402
+from point_cloud_segmentation_b200.distributed import MapExchange, PeerMapExchange  # noqa: E402
+
+
+def main():
+    rank, world, local_rank = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    out_dir = os.environ["OUT_DIR"]
+    torch.cuda.set_device(local_rank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = pcs.Context(local_rank, torch.cuda.current_stream().cuda_stream)
+    w, h, res, per_rank, cap = 320, 240, 0.005, 3, 1 << 18
+    first = rank * per_rank
+    poses = np.stack([bench.synth_pose(first + f) for f in range(per_rank)])
+    d_pose, d_in = ctx.dev_alloc(poses.nbytes), ctx.dev_alloc(per_rank * w * h * 32)
+    ctx.h2d(d_pose, poses)
+    ctx.synth_frames_dev(bench.SEED, first, per_rank, w, h, d_pose, d_in)
+    local = ctx.create_map(res, cap)
+    ctx.annotate_frames_dev(d_in, per_rank, w, h, d_pose, pcs.annotate_params(lower=255, upper=255), local, None, None)
+
+    nccl = MapExchange(ctx, local, dist, torch, cap)
+    nccl.exchange()
+    nccl.exchange()  # repeatable
+    k1, a1, b1, _ = nccl._owned_map.export()
+    full = ctx.create_map(res, cap)
+    from point_cloud_segmentation_b200.distributed import GpuMapAdapter
+
+    nccl.allgather_owned(GpuMapAdapter(ctx, full))
+    kf, af, bf, _ = full.export()
+
+    peer = PeerMapExchange(ctx, local, dist, torch, cap)
+    peer.exchange()
+    peer.exchange()
+    ctx.sync()
+    k2, a2, b2, _ = peer.owned_map.export()
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), k1=k1, a1=a1, b1=b1, k2=k2, a2=a2, b2=b2, kf=kf, af=af, bf=bf)
+    peer.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -125,3 +125,32 @@ def test_empty_map_and_bad_args(ctx, pcs):
     with pytest.raises(pcs.PcsError):
         ctx.create_map(0.0, 16)
     vmap.destroy()
+
+
+def test_push_to_owners_partitions_the_map(ctx, pcs, O):
+    """Peer-memory exchange kernel with the owner tables in this process: the owners' slices partition the local map by
+    mix64(key48) % n_owners and their union equals it (the multi-GPU run maps the same tables through CUDA IPC)."""
+    rng = np.random.default_rng(21)
+    cloud = random_cloud(pcs.POINT_DTYPE, 60000, rng, extent=0.6)
+    local = ctx.create_map(0.01, 1 << 17)
+    local.integrate(cloud, None, 0, 120)
+    want = local.export()
+    for n_owners in (1, 3, 8):
+        owners = [ctx.create_map(0.01, 1 << 17) for _ in range(n_owners)]
+        local.push_to_owners_dev(owners)
+        local.push_to_owners_dev(owners)  # pushing twice doubles every counter: adds, not overwrites
+        total = ctx.create_map(0.01, 1 << 17)
+        n_seen = 0
+        for o, m in enumerate(owners):
+            k, c0, c1, _ = m.export()
+            assert all(pcs.capi.mix64(int(x)) % n_owners == o for x in k[:: max(1, k.size // 200)])
+            n_seen += k.size
+            total.merge(k, c0, c1)
+        assert n_seen == want[0].size
+        k, c0, c1, _ = total.export()
+        assert np.array_equal(k, want[0]) and np.array_equal(c0, 2 * want[1]) and np.array_equal(c1, 2 * want[2])
+        for m in owners + [total]:
+            m.destroy()
+    with pytest.raises(pcs.PcsError):
+        local.push_to_owners_dev([local])
+    local.destroy()
