@@ -180,6 +180,7 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=200, help="frames of the cpu_baseline sample")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="multi-GPU map exchange: one kernel over NVLink peer memory, or NCCL all-to-all of records")
+    ap.add_argument("--exchange-debug", default="", choices=["", "setup-only", "barriers-only"], help=argparse.SUPPRESS)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mesh", action="store_true")
@@ -202,7 +203,10 @@ def main():
 
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        stream_handle = torch.cuda.current_stream().cuda_stream
+        # kernels of libpcs_b200 and NCCL collectives must be ordered: one shared, non-default stream for both
+        shared_stream = torch.cuda.Stream()
+        torch.cuda.set_stream(shared_stream)
+        stream_handle = shared_stream.cuda_stream
     else:
         stream_handle = None
 
@@ -255,7 +259,11 @@ def main():
         if timed_kernel is not None:
             ctx.record(timed_kernel[1])
         if exch is not None:
-            exch.exchange()
+            if args.exchange_debug == "barriers-only":
+                exch._barrier()
+                exch._barrier()
+            elif args.exchange_debug != "setup-only":
+                exch.exchange()
 
     def barrier():
         ctx.sync()

@@ -286,6 +286,7 @@ class Context:
         _check(self.lib.pcs_ctx_create(int(device), _p(cuda_stream), C.byref(h)))
         self.h = h
         self.device = device
+        self.cuda_stream = int(cuda_stream) if cuda_stream else None  # None: the library created its own stream
 
     def destroy(self):
         if self.h:

@@ -27,6 +27,17 @@ import numpy as np
 RECORD_BYTES = 16
 
 
+def check_shared_stream(ctx, torch):
+    """The exchange interleaves libpcs_b200 kernels with torch.distributed collectives; they are only ordered if both
+    are enqueued on the same CUDA stream.  A context created with cuda_stream=None (or with torch's legacy default
+    stream, whose handle is 0) runs on a private stream and would race with the collectives."""
+    cur = torch.cuda.current_stream().cuda_stream
+    if not ctx.cuda_stream or ctx.cuda_stream != cur:
+        raise ValueError(
+            "pcs context and torch must share one non-default CUDA stream: create `s = torch.cuda.Stream()`, "
+            "`torch.cuda.set_stream(s)` and `Context(device, s.cuda_stream)` before building the exchange")
+
+
 class GpuMapAdapter:
     """Adapts a capi.VoxelMap (device hash) to the exchange: records live in torch CUDA tensors."""
 
@@ -57,6 +68,7 @@ class MapExchange:
         self.world = dist.get_world_size()
         self.rank = dist.get_rank()
         if local is None:
+            check_shared_stream(ctx, torch)
             local = GpuMapAdapter(ctx, vmap)
             self._owned_map = ctx.create_map(vmap.resolution, capacity_voxels)
             owned = GpuMapAdapter(ctx, self._owned_map)
@@ -132,6 +144,7 @@ class PeerMapExchange:
     def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int):
         from . import capi
 
+        check_shared_stream(ctx, torch)
         self.ctx, self.local, self.dist, self.torch = ctx, vmap, dist, torch
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         self.device = torch.device("cuda", ctx.device)

@@ -24,7 +24,9 @@ def main():
     out_dir = os.environ["OUT_DIR"]
     torch.cuda.set_device(local_rank)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    ctx = pcs.Context(local_rank, torch.cuda.current_stream().cuda_stream)
+    shared_stream = torch.cuda.Stream()  # libpcs_b200 kernels and NCCL collectives are ordered on this one stream
+    torch.cuda.set_stream(shared_stream)
+    ctx = pcs.Context(local_rank, shared_stream.cuda_stream)
     w, h, res, per_rank, cap = 320, 240, 0.005, 3, 1 << 18
     first = rank * per_rank
     poses = np.stack([bench.synth_pose(first + f) for f in range(per_rank)])
