@@ -214,6 +214,15 @@ PCS_API int pcs_map_size(pcs_ctx* ctx, pcs_map* map, uint64_t* n_voxels, uint64_
  * reported and PCS_ERR_CAPACITY returned (two-call size query). */
 PCS_API int pcs_map_export(pcs_ctx* ctx, pcs_map* map, uint64_t cap, uint64_t* key48, uint32_t* count0,
                            uint32_t* count1, float* logodds, uint64_t* n);
+/* OcTree-compatible views of the map.
+ * pcs_map_write_bt: the occupied voxels (count1 >= 1) as an octomap binary tree, byte-compatible with
+ * octomap::OcTree::writeBinary for the same occupied set -- the format the reference's test reads with
+ * octomap::OcTree(path) (pcs_scan_integration/test/octomap_mesh_masking_unit.cpp:140-141).  out == NULL queries the size.
+ * pcs_map_leaf_centers: one point per voxel at the voxel centre, in octree order, r = g = b = 255 where count1 >= 1 else
+ * 0 (alpha 255): the colourised centre cloud the mesh-mask action consumes
+ * (pcs_ros/src/octomap_mesh_mask_node.cpp:47-68).  points == NULL queries the count. */
+PCS_API int pcs_map_write_bt(pcs_ctx* ctx, pcs_map* map, uint8_t* out, uint64_t cap, uint64_t* n_bytes);
+PCS_API int pcs_map_leaf_centers(pcs_ctx* ctx, pcs_map* map, uint64_t cap, pcs_point_xyzrgb* points, uint64_t* n_out);
 /* Import / merge records (checkpoint restore, multi-GPU merge): counters are added to existing voxels. */
 PCS_API int pcs_map_merge(pcs_ctx* ctx, pcs_map* map, const uint64_t* key48, const uint32_t* count0,
                           const uint32_t* count1, uint64_t n);

@@ -87,6 +87,8 @@ SIGNATURES = {
     "pcs_map_integrate_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _i, _i, _i]),
     "pcs_map_size": (_i, [_vp, _vp, _pu64, _pu64]),
     "pcs_map_export": (_i, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _pu64]),
+    "pcs_map_write_bt": (_i, [_vp, _vp, _vp, _u64, _pu64]),
+    "pcs_map_leaf_centers": (_i, [_vp, _vp, _u64, _vp, _pu64]),
     "pcs_map_merge": (_i, [_vp, _vp, _vp, _vp, _vp, _u64]),
     "pcs_map_pack_by_owner_dev": (_i, [_vp, _vp, _i, _vp, _u64, _vp]),
     "pcs_map_merge_records_dev": (_i, [_vp, _vp, _vp, _u64]),
@@ -240,6 +242,22 @@ class VoxelMap:
         if m:
             _check(self.ctx.lib.pcs_map_export(self.ctx.h, self.h, m, _p(k), _p(c0), _p(c1), _p(lo), C.byref(n)))
         return k, c0, c1, lo
+
+    def write_bt(self) -> bytes:
+        """Occupied voxels as an octomap binary tree (.bt) file image."""
+        n = C.c_uint64(0)
+        _check(self.ctx.lib.pcs_map_write_bt(self.ctx.h, self.h, None, 0, C.byref(n)))
+        buf = np.empty(int(n.value), np.uint8)
+        _check(self.ctx.lib.pcs_map_write_bt(self.ctx.h, self.h, _p(buf), buf.size, C.byref(n)))
+        return buf.tobytes()
+
+    def leaf_centers(self) -> np.ndarray:
+        n = C.c_uint64(0)
+        _check(self.ctx.lib.pcs_map_leaf_centers(self.ctx.h, self.h, 0, None, C.byref(n)))
+        pts = np.empty(int(n.value), POINT_DTYPE)
+        if pts.size:
+            _check(self.ctx.lib.pcs_map_leaf_centers(self.ctx.h, self.h, pts.size, _p(pts), C.byref(n)))
+        return pts
 
     def merge(self, key48, count0, count1):
         k = _c(key48, np.uint64)

@@ -79,6 +79,20 @@ public:
     return no;
   }
 
+  /** @brief octomap::OcTree::writeBinary: the occupied voxels as a .bt file. */
+  bool writeBinary(const std::string& path) const
+  {
+    uint64_t n = 0;
+    if (pcs_map_write_bt(pcs_compat::default_ctx(), map_, nullptr, 0, &n) != PCS_OK)
+      return false;
+    std::vector<uint8_t> bytes(n);
+    if (pcs_map_write_bt(pcs_compat::default_ctx(), map_, bytes.data(), n, &n) != PCS_OK)
+      return false;
+    std::ofstream f(path, std::ios::binary);
+    f.write(reinterpret_cast<const char*>(bytes.data()), static_cast<std::streamsize>(bytes.size()));
+    return !f.fail();
+  }
+
 private:
   void create(std::size_t capacity)
   {

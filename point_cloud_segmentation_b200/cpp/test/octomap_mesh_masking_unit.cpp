@@ -104,6 +104,16 @@ TEST(OctomapMeshMaskUnit, maskMesh)
   std::string path = DATA_DIR() + "/box_2m.bt";
   Octree::Ptr octree(new Octree(path));
   masker.setOctree(octree);
+  {
+    // .bt round trip: what was read is written back byte for byte
+    const std::string copy = DATA_DIR() + "/box_2m_copy.bt";
+    EXPECT_TRUE(octree->writeBinary(copy));
+    std::vector<uint8_t> a, b;
+    EXPECT_TRUE(pcs_compat::readFile(path, a));
+    EXPECT_TRUE(pcs_compat::readFile(copy, b));
+    EXPECT_TRUE(a == b);
+    EXPECT_EQ(octree->occupiedVoxels(), 64u);
+  }
   Mesh::Ptr mesh = pcs_compat::createMeshFromPath(DATA_DIR() + "/plane_4m.stl");
   masker.setInputMesh(mesh);
   {
