@@ -136,6 +136,16 @@ PCS_API int pcs_hsv_mask_dev(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, in
 PCS_API int pcs_hsv_annotation_image(pcs_ctx* ctx, const uint8_t* bgr, int width, int height, size_t stride,
                                      const pcs_hsv_params* params, uint8_t* annotation_bgr);
 
+/* Replaces HistogramBackprojection.annotate_image
+ * (pcs_detection/src_python/pcs_detection/models/histogram_backprojection.py:22-52; service in
+ * pcs_ros/src/histogram_backprojection_node:29-44): BGR2HSV, calcBackProject of the (hue, saturation) histogram
+ * (h_bins x s_bins float32, row-major, ranges [0,180) x [0,255)), 5x5 ellipse filter2D, threshold (> threshold_min ->
+ * threshold_value; the reference uses 30 and 150), 5x5 opening, min-max normalisation to {0, 255}, three equal channels.
+ * 8UC3 in (row pitch `stride`) -> 8UC3 out, tightly packed. */
+PCS_API int pcs_histogram_backprojection(pcs_ctx* ctx, const uint8_t* bgr, int width, int height, size_t stride,
+                                         const float* histogram, int h_bins, int s_bins, int threshold_min,
+                                         int threshold_value, uint8_t* annotation_bgr);
+
 /* ---- stage 2: organized cloud <-> images, labelling, transform -------------------------------------------------- */
 /* Replaces pcs_detection::cloudToImage (pcs_detection/include/pcs_detection/utils.h:98-129): organized cloud ->
  * CV_64FC3 position image (h*w*3 doubles) + CV_8UC3 BGR image (h*w*3 bytes).  1x1 clouds are rejected (:103). */

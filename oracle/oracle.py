@@ -56,6 +56,7 @@ def lib() -> C.CDLL:
             "orc_hsv_mask": (None, [vp, i32, i32, sz, C.POINTER(HsvParams), vp, sz]),
             "orc_morph_open5": (None, [vp, i32, i32, vp]),
             "orc_hsv_exhaustive_hash": (u64, [C.POINTER(HsvParams), C.POINTER(u64)]),
+            "orc_histogram_backprojection": (None, [vp, i32, i32, sz, vp, i32, i32, i32, i32, vp]),
             "orc_cloud_to_image": (None, [vp, i32, i32, vp, vp]),
             "orc_image_to_cloud": (None, [vp, vp, i32, i32, vp]),
             "orc_color_passthrough": (sz, [vp, sz, i32, i32, i32, vp]),
@@ -153,6 +154,16 @@ def hsv_exhaustive_hash(params: HsvParams | None = None):
     n = C.c_uint64(0)
     hsh = lib().orc_hsv_exhaustive_hash(C.byref(p), C.byref(n))
     return int(hsh), int(n.value)
+
+
+def histogram_backprojection(bgr: np.ndarray, hist: np.ndarray, thr_min: int = 30, thr_value: int = 150) -> np.ndarray:
+    bgr = _c(bgr, np.uint8)
+    hist = _c(hist, np.float32)
+    h, w, _ = bgr.shape
+    out = np.empty((h, w, 3), np.uint8)
+    lib().orc_histogram_backprojection(_p(bgr), w, h, w * 3, _p(hist), hist.shape[0], hist.shape[1], thr_min, thr_value,
+                                       _p(out))
+    return out
 
 
 # ---- stage 2 -------------------------------------------------------------------------------------------

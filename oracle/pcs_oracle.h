@@ -61,6 +61,13 @@ void orc_morph_open5(const uint8_t* in, int w, int h, uint8_t* out);
 /* hash of the mask over all 2^24 BGR colours (b fastest), FNV-1a 64 */
 uint64_t orc_hsv_exhaustive_hash(const orc_hsv_params* p, uint64_t* n_positive);
 
+/* histogram back-projection detector (pcs_detection/src_python/pcs_detection/models/histogram_backprojection.py:22-52):
+ * BGR2HSV, calcBackProject on (H,S) with ranges [0,180),[0,255), 5x5 ellipse filter2D, threshold, 5x5 open, min-max
+ * normalise to {0,1}, x255, 3 channels.  hist is h_bins x s_bins float32, row-major. */
+void orc_backproject_tables(int h_bins, int s_bins, int32_t tab_h[256], int32_t tab_s[256]);
+void orc_histogram_backprojection(const uint8_t* bgr, int w, int h, size_t stride, const float* hist, int h_bins,
+                                  int s_bins, int thr_min, int thr_value, uint8_t* out_bgr3);
+
 /* ---- stage 2: cloud <-> image, labelling ---------------------------------------------- */
 void orc_cloud_to_image(const orc_point* cloud, int w, int h, double* position_image, uint8_t* bgr_image);
 void orc_image_to_cloud(const uint8_t* annotation_bgr, const double* position_image, int w, int h, orc_point* out);

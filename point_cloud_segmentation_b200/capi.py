@@ -73,6 +73,7 @@ SIGNATURES = {
     "pcs_hsv_mask": (_i, [_vp, _vp, _i, _i, _sz, C.POINTER(HsvParams), _vp, _sz]),
     "pcs_hsv_mask_dev": (_i, [_vp, _vp, _i, _i, _sz, C.POINTER(HsvParams), _vp, _sz]),
     "pcs_hsv_annotation_image": (_i, [_vp, _vp, _i, _i, _sz, C.POINTER(HsvParams), _vp]),
+    "pcs_histogram_backprojection": (_i, [_vp, _vp, _i, _i, _sz, _vp, _i, _i, _i, _i, _vp]),
     "pcs_cloud_to_image": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "pcs_image_to_cloud": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "pcs_color_passthrough": (_i, [_vp, _vp, _u64, _i, _i, _i, _vp, _pu64]),
@@ -382,6 +383,17 @@ class Context:
         out = np.empty((h, w, 3), np.uint8)
         p = params or hsv_params()
         _check(self.lib.pcs_hsv_annotation_image(self.h, _p(bgr), w, h, bgr.strides[0], C.byref(p), _p(out)))
+        return out
+
+    def histogram_backprojection(self, bgr: np.ndarray, hist: np.ndarray, threshold_min: int = 30,
+                                 threshold_value: int = 150) -> np.ndarray:
+        """HistogramBackprojection.annotate_image: (h, w, 3) BGR + (h_bins, s_bins) float32 histogram -> (h, w, 3) mask."""
+        assert bgr.dtype == np.uint8 and bgr.ndim == 3 and bgr.shape[2] == 3 and bgr.strides[1:] == (3, 1)
+        hist = _c(hist, np.float32)
+        h, w, _ = bgr.shape
+        out = np.empty((h, w, 3), np.uint8)
+        _check(self.lib.pcs_histogram_backprojection(self.h, _p(bgr), w, h, bgr.strides[0], _p(hist), hist.shape[0],
+                                                     hist.shape[1], int(threshold_min), int(threshold_value), _p(out)))
         return out
 
     # ---- stage 2 -----------------------------------------------------------------------------------------------

@@ -57,6 +57,18 @@ struct HsvBounds
   int h_lo, h_hi, s_lo, s_hi, v_lo, v_hi;
 };
 
+// hue [0,179] and saturation [0,255] of a pixel (the two channels the histogram detector back-projects)
+__device__ __forceinline__ void bgr_to_hs(const int* __restrict__ s_lut, int b, int g, int r, int& h, int& s)
+{
+  const int v = max(max(b, g), r);
+  const int vmin = min(min(b, g), r);
+  const int diff = v - vmin;
+  s = (diff * s_lut[v] + 2048) >> 12;
+  h = (v == r) ? (g - b) : ((v == g) ? (b - r + 2 * diff) : (r - g + 4 * diff));
+  h = (h * s_lut[256 + diff] + 2048) >> 12;
+  h += (h < 0) ? 180 : 0;
+}
+
 // returns true when (h,s,v) of the pixel lies inside the inclusive bounds
 __device__ __forceinline__ bool hsv_in_range(const int* __restrict__ s_lut, int b, int g, int r, const HsvBounds& p)
 {

@@ -88,6 +88,52 @@ def fixture_golden():
     print("reference_fixtures.npz: plane", v.shape, f.shape, "box", pv.shape, pf.shape, "bt leaves", len(kx))
 
 
+def backproject_golden():
+    """cv2 outputs of HistogramBackprojection.annotate_image
+    (pcs_detection/src_python/pcs_detection/models/histogram_backprojection.py:22-52) for trained histograms of
+    several bin counts."""
+    import cv2
+
+    def annotate(img, hist):
+        hsv = cv2.cvtColor(img, cv2.COLOR_BGR2HSV)
+        dst = cv2.calcBackProject([hsv], [0, 1], hist, [0, 180, 0, 255], 1)
+        disc = cv2.getStructuringElement(cv2.MORPH_ELLIPSE, (5, 5))
+        cv2.filter2D(dst, -1, disc, dst)
+        _, t = cv2.threshold(dst, 30, 150, 0)
+        c = cv2.morphologyEx(t, cv2.MORPH_OPEN, np.ones((5, 5), np.uint8))
+        cv2.normalize(c, c, 0, 1, cv2.NORM_MINMAX, cv2.CV_8UC3)
+        c = 255 * c
+        return cv2.merge((c, c, c))
+
+    rng = np.random.default_rng(20191002)
+    out = {}
+    cases = []
+    for hi, (nh, ns) in enumerate([(180, 256), (30, 32), (50, 60)]):
+        sample = np.zeros((40, 40, 3), np.uint8)
+        sample[:] = (140, 90, 50)
+        sample = (sample.astype(int) + rng.integers(-20, 20, sample.shape)).clip(0, 255).astype(np.uint8)
+        hist = cv2.calcHist([cv2.cvtColor(sample, cv2.COLOR_BGR2HSV)], [0, 1], None, [nh, ns], [0, 180, 0, 255])
+        cv2.normalize(hist, hist, 0, 255, cv2.NORM_MINMAX)
+        out[f"hist{hi}"] = hist
+        for si, shape in enumerate([(37, 53), (3, 3), (120, 160)]):
+            img = rng.integers(0, 256, (*shape, 3), dtype=np.uint8)
+            for _ in range(5):
+                y0, x0 = rng.integers(0, shape[0]), rng.integers(0, shape[1])
+                img[y0:y0 + rng.integers(1, 30), x0:x0 + rng.integers(1, 30)] = (140, 90, 50)
+            img[..., 1][img[..., 1] == 90] = 255
+            out[f"img{hi}_{si}"] = img
+            out[f"out{hi}_{si}"] = annotate(img, hist)
+            cases.append((hi, si))
+        const = np.zeros((20, 20, 3), np.uint8)
+        const[:] = (140, 90, 50)
+        out[f"img{hi}_c"] = const
+        out[f"out{hi}_c"] = annotate(const, hist)  # all detected -> min == max -> normalises to zeros
+    out["cases"] = np.array(cases)
+    np.savez_compressed(os.path.join(HERE, "backproject_cv2.npz"), **out)
+    print("backproject_cv2.npz:", len(cases), "cases")
+
+
 if __name__ == "__main__":
+    backproject_golden()
     hsv_golden()
     fixture_golden()
