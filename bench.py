@@ -453,13 +453,23 @@ def run_mesh(ctx, pcs, vmap, n_frames, peak):
     ctx.h2d(d_f, faces)
     for _ in range(3):
         ctx.mesh_contacts_dev(vmap, d_v, nv, d_f, nt, d_fl)
-    e0, e1 = ctx.event(), ctx.event()
+    # the mesh (58 MB) fits in L2: flush it before every timed launch by writing a 512 MB buffer
+    flush_bytes = 512 << 20
+    d_flush = ctx.dev_alloc(flush_bytes)
     reps = 10
-    ctx.record(e0)
-    for _ in range(reps):
+    evs = [(ctx.event(), ctx.event()) for _ in range(reps)]
+    for a, b in evs:
+        ctx.memset(d_flush, 0, flush_bytes)
+        ctx.record(a)
         ctx.mesh_contacts_dev(vmap, d_v, nv, d_f, nt, d_fl)
-    ctx.record(e1)
-    ms = ctx.elapsed_ms(e0, e1) / reps
+        ctx.record(b)
+    ctx.sync()
+    ms = float(np.mean([ctx.elapsed_ms(a, b) for a, b in evs]))
+    for a, b in evs:
+        ctx.event_destroy(a)
+        ctx.event_destroy(b)
+    ctx.dev_free(d_flush)
+    e0, e1 = ctx.event(), ctx.event()
     flags = np.empty(nt, np.uint8)
     ctx.d2h(flags, d_fl)
     s = float(flags.mean())
@@ -467,7 +477,7 @@ def run_mesh(ctx, pcs, vmap, n_frames, peak):
     out = {"metric": "mesh-mask triangles/sec", "value": nt / (ms * 1e-3), "unit": "tris/s", "triangles": nt,
            "ms": ms, "inside_fraction": s, "achieved_gbs": bytes_per_tri * nt / (ms * 1e-3) / 1e9,
            "frac_of_hbm_peak": bytes_per_tri * nt / (ms * 1e-3) / 1e9 / peak,
-           "note": "flags-only device-resident pass; tiny input (58 MB) is L2-resident, so this is latency/L2-bound"}
+           "note": "flags-only device-resident pass, L2 flushed (512 MB memset) before every timed launch; map lookups hit L2"}
     for p in (d_v, d_f, d_fl):
         ctx.dev_free(p)
     ctx.event_destroy(e0)

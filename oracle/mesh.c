@@ -64,6 +64,12 @@ int orc_tri_box_overlap(const double lo[3], const double hi[3], const double v0[
     if (!(mn <= hi[a]) || !(mx >= lo[a])) /* NaN vertices never overlap */
       return 0;
   }
+  /* a vertex inside the closed box is a contact outright (exact comparisons, no rounding involved) */
+  const double* vs[3] = { v0, v1, v2 };
+  for (int i = 0; i < 3; i++)
+    if (vs[i][0] >= lo[0] && vs[i][0] <= hi[0] && vs[i][1] >= lo[1] && vs[i][1] <= hi[1] && vs[i][2] >= lo[2] &&
+        vs[i][2] <= hi[2])
+      return 1;
   double c[3], h[3], p0[3], p1[3], p2[3], e0[3], e1[3], e2[3];
   for (int a = 0; a < 3; a++)
   {

@@ -43,6 +43,11 @@ __device__ __forceinline__ bool axis_separates(double ax, double ay, double az, 
   return (mn > r) || (mx < -r);
 }
 
+__device__ __forceinline__ bool point_in_box(const double* lo, const double* hi, const double* v)
+{
+  return v[0] >= lo[0] && v[0] <= hi[0] && v[1] >= lo[1] && v[1] <= hi[1] && v[2] >= lo[2] && v[2] <= hi[2];
+}
+
 // closed triangle / axis-aligned box overlap; same operation order as orc_tri_box_overlap
 __device__ bool tri_box_overlap(const double* lo, const double* hi, const double* v0, const double* v1, const double* v2)
 {
@@ -53,6 +58,9 @@ __device__ bool tri_box_overlap(const double* lo, const double* hi, const double
     if (!(mn <= hi[a]) || !(mx >= lo[a]))
       return false;
   }
+  // a vertex inside the closed box is a contact outright (exact comparisons, no rounding involved)
+  if (point_in_box(lo, hi, v0) || point_in_box(lo, hi, v1) || point_in_box(lo, hi, v2))
+    return true;
   double c[3], h[3], p0[3], p1[3], p2[3], e0[3], e1[3], e2[3];
 #pragma unroll
   for (int a = 0; a < 3; a++)
@@ -162,40 +170,92 @@ __device__ __forceinline__ void load_tri(const double* __restrict__ verts, unsig
     d.ok = key_range(dmin3(d.v0[a], d.v1[a], d.v2[a]), dmax3(d.v0[a], d.v1[a], d.v2[a]), res, inv, d.lo[a], d.hi[a]) && d.ok;
 }
 
-__global__ void __launch_bounds__(128) mesh_contacts_kernel(MapView m, double res, const double* __restrict__ verts,
-                                                           unsigned long long nv, const int* __restrict__ faces4,
-                                                           unsigned long long nt, uint8_t* __restrict__ flags,
-                                                           unsigned int* __restrict__ big_list,
-                                                           unsigned int* __restrict__ big_count)
+// Pass 1 (lean, high occupancy): the voxel that holds a vertex decides most triangles of a mesh finer than the voxels
+// with one table probe each and no SAT.  Undecided triangles go to a to-do list for pass 2.
+__global__ void __launch_bounds__(256, 4) mesh_vertex_probe_kernel(MapView m, double res, const double* __restrict__ verts,
+                                                                  unsigned long long nv, const int* __restrict__ faces4,
+                                                                  unsigned long long nt, uint8_t* __restrict__ flags,
+                                                                  unsigned int* __restrict__ todo,
+                                                                  unsigned int* __restrict__ todo_count)
 {
   const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= nt)
     return;
-  TriData d;
-  load_tri(verts, nv, faces4, t, res, m.inv_res, d);
+  const int4 f = __ldg(reinterpret_cast<const int4*>(faces4) + t);
+  const bool ok = f.y >= 0 && f.z >= 0 && f.w >= 0 && (unsigned long long)f.y < nv && (unsigned long long)f.z < nv &&
+                  (unsigned long long)f.w < nv;
   uint8_t flag = 0;
-  if (d.ok)
+  if (ok)
   {
+    const int idx[3] = { f.y, f.z, f.w };
+    bool finite = true;
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+    {
+      double v[3];
+      int k[3];
+      bool inside = true;
+#pragma unroll
+      for (int a = 0; a < 3; a++)
+      {
+        v[a] = __ldg(verts + 3ull * idx[i] + a);
+        finite = finite && isfinite(v[a]);
+        const double e = fmin(fmax(floor(v[a] * m.inv_res), -32768.0), 32767.0);
+        k[a] = (int)e + 32768;
+        inside = inside && v[a] >= vox_lo(k[a], res) && v[a] <= vox_hi(k[a], res);  // exact test guards the estimate
+      }
+      if (!flag && inside &&
+          map_occupied(m, ((unsigned long long)k[2] << 32) | ((unsigned long long)k[1] << 16) | (unsigned long long)k[0]))
+        flag = 1;
+    }
+    if (!finite)
+      flag = 0;  // a triangle with a non-finite vertex touches nothing (same rule as the key-range walk)
+    else if (!flag)
+      todo[atomicAdd(todo_count, 1u)] = (unsigned int)t;
+  }
+  flags[t] = flag;
+}
+
+// Pass 2: triangles the vertex probe could not decide walk the voxel keys their bounding box covers and run the closed
+// separating-axis test against the occupied ones.
+__global__ void __launch_bounds__(128) mesh_contacts_kernel(MapView m, double res, const double* __restrict__ verts,
+                                                           unsigned long long nv, const int* __restrict__ faces4,
+                                                           uint8_t* __restrict__ flags, const unsigned int* __restrict__ todo,
+                                                           const unsigned int* __restrict__ todo_count,
+                                                           unsigned int* __restrict__ big_list,
+                                                           unsigned int* __restrict__ big_count)
+{
+  const unsigned int n_todo = *todo_count;
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_todo; i += gridDim.x * blockDim.x)
+  {
+    const unsigned long long t = todo[i];
+    TriData d;
+    load_tri(verts, nv, faces4, t, res, m.inv_res, d);
+    if (!d.ok)
+      continue;
     const unsigned long long vol = (unsigned long long)(d.hi[0] - d.lo[0] + 1) * (unsigned long long)(d.hi[1] - d.lo[1] + 1) *
                                    (unsigned long long)(d.hi[2] - d.lo[2] + 1);
     if (vol > kInlineRangeLimit)
+    {
       big_list[atomicAdd(big_count, 1u)] = (unsigned int)t;  // handled voxel-major by mesh_contacts_big_kernel
-    else
-      for (int kz = d.lo[2]; kz <= d.hi[2] && !flag; kz++)
-        for (int ky = d.lo[1]; ky <= d.hi[1] && !flag; ky++)
-          for (int kx = d.lo[0]; kx <= d.hi[0] && !flag; kx++)
-          {
-            const unsigned long long key =
-                ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | (unsigned long long)kx;
-            if (!map_occupied(m, key))
-              continue;
-            const double blo[3] = { vox_lo(kx, res), vox_lo(ky, res), vox_lo(kz, res) };
-            const double bhi[3] = { vox_hi(kx, res), vox_hi(ky, res), vox_hi(kz, res) };
-            if (tri_box_overlap(blo, bhi, d.v0, d.v1, d.v2))
-              flag = 1;
-          }
+      continue;
+    }
+    uint8_t flag = 0;
+    for (int kz = d.lo[2]; kz <= d.hi[2] && !flag; kz++)
+      for (int ky = d.lo[1]; ky <= d.hi[1] && !flag; ky++)
+        for (int kx = d.lo[0]; kx <= d.hi[0] && !flag; kx++)
+        {
+          const unsigned long long key = ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | (unsigned long long)kx;
+          if (!map_occupied(m, key))
+            continue;
+          const double blo[3] = { vox_lo(kx, res), vox_lo(ky, res), vox_lo(kz, res) };
+          const double bhi[3] = { vox_hi(kx, res), vox_hi(ky, res), vox_hi(kz, res) };
+          if (tri_box_overlap(blo, bhi, d.v0, d.v1, d.v2))
+            flag = 1;
+        }
+    if (flag)
+      flags[t] = 1;
   }
-  flags[t] = flag;
 }
 
 // triangles whose key range is too large to walk: every occupied voxel tests itself against each of them
@@ -305,21 +365,28 @@ __global__ void colorize_kernel(const uint8_t* __restrict__ flags, const int* __
 int mesh_contacts_launch(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev,
                          uint64_t nt, uint8_t* flags_dev)
 {
-  // scratch: [counter (16 B)] [big list: nt u32]
+  // scratch: [todo_count, big_count (16 B)] [todo list: nt u32] [big list: nt u32]
   void* scr = nullptr;
-  PCS_TRY(ctx_scratch(ctx, 16 + nt * sizeof(unsigned int), &scr));
-  unsigned int* big_count = (unsigned int*)scr;
-  unsigned int* big_list = (unsigned int*)((char*)scr + 16);
-  PCS_CUDA(cudaMemsetAsync(big_count, 0, 16, ctx->stream));
-  mesh_contacts_kernel<<<(unsigned int)((nt + 127) / 128), 128, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv,
-                                                                                 faces4_dev, nt, flags_dev, big_list, big_count);
-  unsigned long long blocks = (map->n_slots + 255) / 256;
+  PCS_TRY(ctx_scratch(ctx, 16 + 2 * nt * sizeof(unsigned int), &scr));
+  unsigned int* todo_count = (unsigned int*)scr;
+  unsigned int* big_count = todo_count + 1;
+  unsigned int* todo = (unsigned int*)((char*)scr + 16);
+  unsigned int* big_list = todo + nt;
+  PCS_CUDA(cudaMemsetAsync(scr, 0, 16, ctx->stream));
   const unsigned long long mx = (unsigned long long)ctx->sm_count * 8ull;
+  mesh_vertex_probe_kernel<<<(unsigned int)((nt + 255) / 256), 256, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv,
+                                                                                     faces4_dev, nt, flags_dev, todo, todo_count);
+  unsigned long long blocks = (nt + 127) / 128;
+  if (blocks > mx)
+    blocks = mx;
+  mesh_contacts_kernel<<<(unsigned int)blocks, 128, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv, faces4_dev,
+                                                                    flags_dev, todo, todo_count, big_list, big_count);
+  blocks = (map->n_slots + 255) / 256;
   if (blocks > mx)
     blocks = mx;
   mesh_contacts_big_kernel<<<(unsigned int)blocks, 256, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv, faces4_dev,
                                                                         flags_dev, big_list, big_count);
-  count_launch(ctx, 2);
+  count_launch(ctx, 3);
   return check_launch("mesh_contacts_kernel");
 }
 }  // namespace pcs
