@@ -75,3 +75,21 @@ def test_fails_loudly_without_cuda(built):
         assert rc == capi.PCS_ERR_CUDA and b"no CPU fallback" in lib.pcs_last_error()
     else:  # running on the GPU box
         lib.pcs_ctx_destroy(h)
+
+
+def test_cmake_project_configures_with_reference_target_names(tmp_path):
+    """CMakeLists.txt exports pcs::pcs_detection_* / pcs::pcs_scan_integration_* like the reference
+    (pcs_detection/CMakeLists.txt:14,35; pcs_scan_integration/CMakeLists.txt:14) -- configure only, no build."""
+    import shutil
+    import subprocess
+
+    if not shutil.which("cmake") or not shutil.which("nvcc"):
+        pytest.skip("cmake / nvcc not available")
+    r = subprocess.run(["cmake", "-S", ROOT, "-B", str(tmp_path), "-DENABLE_TESTS=ON"], capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    text = open(os.path.join(ROOT, "CMakeLists.txt")).read()
+    for tgt in ("pcs_detection_hsv_thresholding", "pcs_detection_point_cloud_annotator",
+                "pcs_scan_integration_octomap_mesh_masking"):
+        assert tgt in text
+    assert "NAMESPACE pcs::" in text and "CMAKE_CUDA_ARCHITECTURES 100a" in text
