@@ -54,7 +54,6 @@ static void prune_leaves(std::vector<Leaf>& leaves)
     std::vector<Leaf> out;
     out.reserve(leaves.size());
     size_t i = 0;
-    bool any = false;
     while (i < leaves.size())
     {
       if (leaves[i].depth == d && (leaves[i].prefix & 7ull) == 0ull && i + 8 <= leaves.size())
@@ -66,14 +65,12 @@ static void prune_leaves(std::vector<Leaf>& leaves)
         {
           out.push_back(Leaf{ leaves[i].prefix >> 3, d - 1 });
           i += 8;
-          any = true;
           continue;
         }
       }
       out.push_back(leaves[i++]);
     }
     leaves.swap(out);
-    (void)any;
   }
 }
 
