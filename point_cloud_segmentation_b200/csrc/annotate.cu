@@ -22,16 +22,19 @@ int launch_hsv_mask(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, int height,
                     const pcs_hsv_params* p, uint8_t* mask_dev, size_t mask_stride, int out_channels);
 
 #ifndef PCS_ANN_UNROLL
-#define PCS_ANN_UNROLL 2
+#define PCS_ANN_UNROLL 1
 #endif
 #ifndef PCS_ANN_ROUNDS
 #define PCS_ANN_ROUNDS 4
 #endif
 #ifndef PCS_ANN_MIN_BLOCKS
-#define PCS_ANN_MIN_BLOCKS 4
+#define PCS_ANN_MIN_BLOCKS 6
 #endif
 #ifndef PCS_ANN_ROUND_UNROLL
 #define PCS_ANN_ROUND_UNROLL 1
+#endif
+#ifndef PCS_ANN_PERSISTENT
+#define PCS_ANN_PERSISTENT 0
 #endif
 #ifndef PCS_ANN_THREADS
 #define PCS_ANN_THREADS 256
@@ -122,10 +125,11 @@ template <bool HAS_MAP, bool WRITE_ANN, bool WRITE_MASK, bool MASK_IN>
 __global__ void __launch_bounds__(kAnnThreads, PCS_ANN_MIN_BLOCKS) annotate_kernel(const AnnotateArgs a)
 {
   __shared__ int s_lut[512];
-  if (!MASK_IN)
-    load_hsv_lut(s_lut);
-  __syncthreads();
+  bool lut_ready = false;
   const bool has_pose = (a.poses != nullptr);
+  // One tile per CTA by default (grid = n_tiles): measured on B200, a plain 32 B/point copy with this tile shape moves
+  // 6.8 TB/s when the hardware block scheduler hands out the tiles and only 6.1 TB/s from 592 persistent CTAs that
+  // stride over them (tools/copy_probe.cu), so the loop below normally runs once.
   for (unsigned int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
   {
     const unsigned int frame = tile / a.tiles_per_frame;
@@ -157,6 +161,14 @@ __global__ void __launch_bounds__(kAnnThreads, PCS_ANN_MIN_BLOCKS) annotate_kern
     for (int u = 0; u < kAnnUnroll; u++)
       if (local + u * kAnnThreads < a.pts_per_frame)
         cur[u] = ld_point_stream(src_pts + local + u * kAnnThreads);
+    if (!lut_ready)
+    {
+      // the detector's tables (2 KB, L2-resident) are fetched while the first points are already in flight
+      if (!MASK_IN)
+        load_hsv_lut(s_lut);
+      __syncthreads();
+      lut_ready = true;
+    }
 #pragma unroll kAnnRoundUnroll
     for (int r = 0; r < kAnnRounds; r++)
     {
@@ -329,8 +341,12 @@ static int launch_annotate(pcs_ctx* ctx, pcs_map* map, const Point8* clouds, uns
   else
     a.map = MapView{ nullptr, 0, nullptr, nullptr, 0.0 };
 
+#if PCS_ANN_PERSISTENT
   const unsigned int max_blocks = (unsigned int)ctx->sm_count * (unsigned int)PCS_ANN_MIN_BLOCKS;  // one resident wave
   const unsigned int grid = a.n_tiles < max_blocks ? a.n_tiles : max_blocks;
+#else
+  const unsigned int grid = a.n_tiles;  // one 2048-point tile per CTA
+#endif
   if (grid == 0)
     return PCS_OK;
   const bool hm = map != nullptr, wa = ann != nullptr, wm = mask != nullptr && mask_in == nullptr, mi = mask_in != nullptr;
