@@ -181,6 +181,7 @@ def main():
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="multi-GPU map exchange: one kernel over NVLink peer memory, or NCCL all-to-all of records")
     ap.add_argument("--exchange-debug", default="", choices=["", "setup-only", "barriers-only"], help=argparse.SUPPRESS)
+    ap.add_argument("--trace", default="", help=argparse.SUPPRESS)  # write per-rank per-step kernel start/end times here
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mesh", action="store_true")
@@ -261,7 +262,6 @@ def main():
         if exch is not None:
             if args.exchange_debug == "barriers-only":
                 exch._barrier()
-                exch._barrier()
             elif args.exchange_debug != "setup-only":
                 exch.exchange()
 
@@ -273,19 +273,34 @@ def main():
 
     for _ in range(max(args.warmup, 1)):
         step()
+    clocks = ClockSampler(local_rank)  # NVML initialisation (milliseconds, varies by rank) stays outside the timed region
     barrier()
 
     launches0 = ctx.stats()["kernel_launches"]
     kernel_ms = [(ctx.event(), ctx.event()) for _ in range(args.steps)]
-    with ClockSampler(local_rank) as clocks:
+    with clocks:
+        if dist is not None:
+            # the host-side barrier releases the ranks up to a few ms apart; one tiny stream-ordered all-reduce lines the
+            # GPU timelines up so that every rank's timed region starts together
+            align = torch.zeros(1, dtype=torch.int32, device="cuda")
+            dist.all_reduce(align)
         ctx.record(ev[0])
+        host_t0, host_ts = time.perf_counter(), []
         for i in range(args.steps):
+            host_ts.append(time.perf_counter() - host_t0)
             step(kernel_ms[i])
         ctx.record(ev[1])
+        host_ts.append(time.perf_counter() - host_t0)
         barrier()
         total_ms = ctx.elapsed_ms(ev[0], ev[1])
     launches = ctx.stats()["kernel_launches"] - launches0
     k_ms = [ctx.elapsed_ms(a, b) for a, b in kernel_ms]
+    if args.trace:
+        tr = {"rank": rank, "kernel_start_ms": [ctx.elapsed_ms(ev[0], a) for a, _ in kernel_ms],
+              "kernel_end_ms": [ctx.elapsed_ms(ev[0], b) for _, b in kernel_ms], "total_ms": total_ms,
+              "host_enqueue_ms": [1e3 * t for t in host_ts]}
+        with open(f"{args.trace}.rank{rank}.json", "w") as f:
+            json.dump(tr, f)
     for a, b in kernel_ms:
         ctx.event_destroy(a)
         ctx.event_destroy(b)

@@ -136,10 +136,13 @@ class MapExchange:
 class PeerMapExchange:
     """Owner-partitioned reduction through peer memory: local voxels are pushed into the owners' tables by one kernel.
 
-    Set-up (once): every rank exports the CUDA IPC handles of its owned map, the handles are all-gathered, and each
-    rank opens its peers' tables.  exchange(): clear the owned slice, barrier (everyone has cleared), push kernel,
-    barrier (every push has landed).  The barriers are 4-byte NCCL all-reduces enqueued on the same stream, so the host
-    never blocks."""
+    Set-up (once): every rank creates TWO owned tables, exports their CUDA IPC handles, the handles are all-gathered and
+    each rank opens its peers' tables.  exchange() number e: clear the table of the other parity (it held the result of
+    exchange e - 1, consumed by now), push kernel into the tables of parity e % 2, one barrier (every push has landed).
+    The double buffer is what makes a single barrier enough: a peer can only push into my parity-(e+1) table after it
+    has passed barrier e, which I enter after my clear of that table has been enqueued.  The barrier is a 4-byte NCCL
+    all-reduce on the shared stream, so the host never blocks.  `owned_map` is the table holding the latest result; it
+    stays valid until the next exchange() call."""
 
     def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int):
         from . import capi
@@ -148,19 +151,24 @@ class PeerMapExchange:
         self.ctx, self.local, self.dist, self.torch = ctx, vmap, dist, torch
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         self.device = torch.device("cuda", ctx.device)
-        self.owned_map = ctx.create_map(vmap.resolution, capacity_voxels)
+        self._mine = [ctx.create_map(vmap.resolution, capacity_voxels) for _ in range(2)]
         ctx.sync()
-        mine = torch.tensor(list(self.owned_map.ipc_export()), dtype=torch.uint8, device=self.device)
-        allh = torch.empty(self.world * 128, dtype=torch.uint8, device=self.device)
+        mine = torch.tensor(list(self._mine[0].ipc_export() + self._mine[1].ipc_export()), dtype=torch.uint8,
+                            device=self.device)
+        allh = torch.empty(self.world * 256, dtype=torch.uint8, device=self.device)
         dist.all_gather_into_tensor(allh, mine)
         allh = allh.cpu().numpy().tobytes()
-        self.owners = []
+        self._owners = [[], []]  # per parity: the table of every rank
         for r in range(self.world):
-            if r == self.rank:
-                self.owners.append(self.owned_map)
-            else:
-                self.owners.append(capi.VoxelMap.ipc_open(ctx, allh[128 * r:128 * (r + 1)], vmap.resolution, capacity_voxels))
+            for b in range(2):
+                if r == self.rank:
+                    self._owners[b].append(self._mine[b])
+                else:
+                    h = allh[256 * r + 128 * b: 256 * r + 128 * (b + 1)]
+                    self._owners[b].append(capi.VoxelMap.ipc_open(ctx, h, vmap.resolution, capacity_voxels))
         self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._epoch = 0
+        self.owned_map = self._mine[0]
         dist.barrier()
 
     @property
@@ -170,19 +178,22 @@ class PeerMapExchange:
     def _barrier(self):
         self.dist.all_reduce(self._token)  # stream-ordered, no host synchronisation
 
-    def exchange(self, clear_owned: bool = True):
-        if clear_owned:
-            self.owned_map.clear()
-        self._barrier()
-        self.local.push_to_owners_dev(self.owners)
-        self._barrier()
+    def exchange(self):
+        b = self._epoch % 2
+        self._mine[1 - b].clear()                      # result of the previous exchange: consumed, recycle it
+        self.local.push_to_owners_dev(self._owners[b])
+        self._barrier()                                # all pushes into parity b have landed everywhere
+        self.owned_map = self._mine[b]
+        self._epoch += 1
 
     def close(self):
         self.ctx.sync()
         self.dist.barrier()
-        for r, m in enumerate(self.owners):
-            if r != self.rank:
-                m.destroy()
-        self.owners = []
+        for b in range(2):
+            for r, m in enumerate(self._owners[b]):
+                if r != self.rank:
+                    m.destroy()
+        self._owners = [[], []]
         self.dist.barrier()
-        self.owned_map.destroy()
+        for m in self._mine:
+            m.destroy()

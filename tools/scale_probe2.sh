@@ -1,4 +1,6 @@
 #!/bin/bash
+# Tuning aid: cost of the pieces of the peer-memory exchange at N GPUs (per-step time with the exchange disabled, with
+# only its barrier, and complete).
 N=${1:-4}
 show() { python -c "
 import json,sys
