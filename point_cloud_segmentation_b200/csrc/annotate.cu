@@ -328,6 +328,12 @@ static int launch_annotate(pcs_ctx* ctx, pcs_map* map, const Point8* clouds, uns
   a.poses = poses;
   a.pts_per_frame = pts_per_frame;
   a.tiles_per_frame = (pts_per_frame + kAnnTile - 1) / kAnnTile;
+  if ((unsigned long long)a.tiles_per_frame * n_frames > 0x7fffffffull)
+  {
+    set_error("batch too large for one launch: %llu tiles (limit 2^31 - 1); split the batch",
+              (unsigned long long)a.tiles_per_frame * n_frames);
+    return PCS_ERR_BAD_ARG;
+  }
   a.n_tiles = a.tiles_per_frame * n_frames;
   a.hsv = HsvBounds{ prm->hsv.h_lo, prm->hsv.h_hi, prm->hsv.s_lo, prm->hsv.s_hi, prm->hsv.v_lo, prm->hsv.v_hi };
   a.inverted = prm->hsv.inverted ? 1 : 0;
@@ -528,10 +534,10 @@ int pcs_map_integrate_dev(pcs_ctx* ctx, pcs_map* map, const pcs_point_xyzrgb* po
   if (n == 0)
     return PCS_OK;
   PCS_CHECK_ARG(points_dev != nullptr, "points is NULL");
+  // one 256-point group per CTA up to 2^31 - 1 CTAs (the hardware block scheduler streams better than a persistent loop)
   unsigned long long blocks = (n + 255) / 256;
-  const unsigned long long max_blocks = (unsigned long long)ctx->sm_count * 8ull;
-  if (blocks > max_blocks)
-    blocks = max_blocks;
+  if (blocks > 0x7fffffffull)
+    blocks = 0x7fffffffull;
   integrate_kernel<<<(unsigned int)blocks, 256, 0, ctx->stream>>>((const Point8*)points_dev, n, pose_dev, lower, upper,
                                                                 limit_negative ? 1 : 0, map->view);
   count_launch(ctx);

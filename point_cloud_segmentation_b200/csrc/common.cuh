@@ -86,6 +86,10 @@ struct pcs_ctx
   size_t pinned_bytes;
   pcs_stats stats;
   int sm_count;
+  // decision tables of the flat HSV image kernel, rebuilt when the thresholds change (hsv.cu)
+  void* hsv_tables_dev;
+  pcs_hsv_params hsv_tables_params;
+  bool hsv_tables_valid;
 };
 
 namespace pcs

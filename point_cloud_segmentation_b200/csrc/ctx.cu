@@ -153,6 +153,8 @@ int pcs_ctx_destroy(pcs_ctx* ctx)
       cudaFree(ctx->staging[i]);
   if (ctx->pinned)
     cudaFreeHost(ctx->pinned);
+  if (ctx->hsv_tables_dev)
+    cudaFree(ctx->hsv_tables_dev);
   for (int i = 0; i < pcs::kCopyStreams; i++)
     cudaStreamDestroy(ctx->copy_stream[i]);
   if (ctx->owns_stream)

@@ -164,6 +164,187 @@ __global__ void __launch_bounds__(kHsvThreads) hsv_mask_kernel(const uint8_t* __
   }
 }
 
+// ---- contiguous fast path -----------------------------------------------------------------------------------------------
+// When the image and the mask are dense (row pitch == row size) and 16-byte aligned, the image is a flat array of
+// pixels.  A CTA takes 4096 pixels: the 12 KiB of BGR bytes are staged in shared memory with coalesced 128-bit loads
+// (lane l fetches bytes [16 l, 16 l + 16) of each 512-byte run), every thread then owns 16 consecutive pixels = three
+// 128-bit shared-memory reads at a 48-byte stride (conflict-free: 12 words per lane, gcd(12, 32) = 4 and a quarter-warp
+// covers all 32 banks), thresholds them in registers and writes its 16 mask bytes with one 128-bit store, so a warp
+// writes 512 contiguous bytes.
+//
+// The per-pixel arithmetic is folded into two small decision tables built on the host for the current thresholds:
+//   vs[v]    = { first diff, number of diffs } for which v and s = (diff * sdiv[v] + 2048) >> 12 are both in range
+//              (s is monotone in diff, so the accepted diffs form one run);
+//   hx[diff] = up to two runs { first X, count } of the hue numerator X = g-b | b-r+2diff | r-g+4diff for which
+//              h = (X * hdiv[diff] + 2048) >> 12 (+180 if negative) is in range (h is monotone in X on either side of
+//              the wrap, so an interval of hues accepts at most two runs of X).
+// Both are enumerated with the exact reference formulas, so the kernel's decisions are the reference's bit for bit; a
+// pixel then costs max3 / min3, the numerator, two table reads and four compares instead of two multiplies, two shifts,
+// a wrap and six compares.
+constexpr int kFastThreads = 256;
+constexpr int kFastPxPerThread = 16;
+constexpr int kFastPxPerCta = kFastThreads * kFastPxPerThread;  // 4096
+
+struct HsvDecisionTables
+{
+  uint32_t vs[256];  // first diff | count << 16
+  int2 hx[256];      // each component: (uint16) first X (two's complement) | count << 16
+};
+
+// false if the thresholds cannot be expressed (never the case for an interval of hues; kept as a guard)
+static bool build_decision_tables(const pcs_hsv_params& p, HsvDecisionTables& t)
+{
+  const HsvLut lut = make_hsv_lut();
+  for (int v = 0; v < 256; v++)
+  {
+    int first = -1, last = -2;
+    for (int diff = 0; diff <= v; diff++)
+    {
+      const int sat = (diff * lut.sdiv[v] + 2048) >> 12;
+      const bool ok = v >= p.v_lo && v <= p.v_hi && sat >= p.s_lo && sat <= p.s_hi;
+      if (ok)
+      {
+        if (first < 0)
+          first = diff;
+        else if (diff != last + 1)
+          return false;
+        last = diff;
+      }
+    }
+    t.vs[v] = first < 0 ? 0u : ((uint32_t)first | ((uint32_t)(last - first + 1) << 16));
+  }
+  for (int diff = 0; diff < 256; diff++)
+  {
+    int start[2] = { 0, 0 }, count[2] = { 0, 0 }, n_runs = 0;
+    bool in_run = false;
+    for (int X = -255; X <= 6 * 255; X++)
+    {
+      int h = (X * lut.hdiv[diff] + 2048) >> 12;  // arithmetic shift on a possibly negative value, as OpenCV
+      if (h < 0)
+        h += 180;
+      const bool ok = h >= p.h_lo && h <= p.h_hi;
+      if (ok && !in_run)
+      {
+        if (n_runs == 2)
+          return false;
+        start[n_runs] = X;
+        count[n_runs] = 0;
+        n_runs++;
+      }
+      if (ok)
+        count[n_runs - 1]++;
+      in_run = ok;
+    }
+    t.hx[diff].x = (int)(((uint32_t)start[0] & 0xffffu) | ((uint32_t)count[0] << 16));
+    t.hx[diff].y = (int)(((uint32_t)start[1] & 0xffffu) | ((uint32_t)count[1] << 16));
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint32_t decide(const uint32_t* __restrict__ s_vs, const int2* __restrict__ s_hx, int b, int g,
+                                           int r)
+{
+  const int v = max(max(b, g), r);
+  const int diff = v - min(min(b, g), r);
+  const int X = (v == r) ? (g - b) : ((v == g) ? (b - r + 2 * diff) : (r - g + 4 * diff));
+  const uint32_t e = s_vs[v];
+  const int2 hh = s_hx[diff];
+  const bool ok_vs = (uint32_t)(diff - (int)(e & 0xffffu)) < (e >> 16);
+  const bool ok_h = ((uint32_t)(X - (int)(short)(hh.x & 0xffff)) < ((uint32_t)hh.x >> 16)) |
+                    ((uint32_t)(X - (int)(short)(hh.y & 0xffff)) < ((uint32_t)hh.y >> 16));
+  return (ok_vs & ok_h) ? 0xffu : 0u;
+}
+
+__global__ void __launch_bounds__(kFastThreads) hsv_mask_flat_kernel(const uint8_t* __restrict__ bgr, unsigned long long n_px,
+                                                                   const HsvDecisionTables* __restrict__ tables,
+                                                                   int inverted, uint8_t* __restrict__ mask)
+{
+  __shared__ uint32_t s_vs[256];
+  __shared__ int2 s_hx[256];
+  __shared__ uint4 s_in[3 * kFastThreads];
+  const unsigned long long px0 = (unsigned long long)blockIdx.x * kFastPxPerCta;
+  const unsigned long long n_bytes = 3ull * n_px, byte0 = 3ull * px0;
+  const uint4* src = reinterpret_cast<const uint4*>(bgr + byte0);
+#pragma unroll
+  for (int j = 0; j < 3; j++)
+  {
+    const unsigned int q = j * kFastThreads + threadIdx.x;  // 16-byte chunk of this CTA's 12 KiB
+    const unsigned long long off = byte0 + 16ull * q;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (off + 16 <= n_bytes)
+      v = __ldg(src + q);
+    else if (off < n_bytes)
+    {
+      // ragged end of the image: byte loads, no read past the buffer
+      uint8_t tmp[16] = { 0 };
+      for (int k = 0; k < 16 && off + k < n_bytes; k++)
+        tmp[k] = bgr[off + k];
+      memcpy(&v, tmp, 16);
+    }
+    s_in[q] = v;
+  }
+  s_vs[threadIdx.x] = __ldg(&tables->vs[threadIdx.x]);
+  s_hx[threadIdx.x] = __ldg(&tables->hx[threadIdx.x]);
+  __syncthreads();
+
+  const unsigned long long first = px0 + (unsigned long long)threadIdx.x * kFastPxPerThread;
+  if (first >= n_px)
+    return;
+  uint32_t w[12];
+#pragma unroll
+  for (int j = 0; j < 3; j++)
+  {
+    const uint4 v = s_in[3 * threadIdx.x + j];
+    w[4 * j + 0] = v.x;
+    w[4 * j + 1] = v.y;
+    w[4 * j + 2] = v.z;
+    w[4 * j + 3] = v.w;
+  }
+  const uint32_t inv = inverted ? 0xffffffffu : 0u;
+  uint32_t out[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++)  // 4 pixels = 12 bytes = 3 words -> 1 output word
+  {
+    const uint32_t a = w[3 * g], b = w[3 * g + 1], c = w[3 * g + 2];
+    // pixel k of the group: bytes 3k, 3k+1, 3k+2 of the 12-byte run (little endian)
+    const uint32_t m0 = decide(s_vs, s_hx, a & 0xff, (a >> 8) & 0xff, (a >> 16) & 0xff);
+    const uint32_t m1 = decide(s_vs, s_hx, a >> 24, b & 0xff, (b >> 8) & 0xff);
+    const uint32_t m2 = decide(s_vs, s_hx, (b >> 16) & 0xff, b >> 24, c & 0xff);
+    const uint32_t m3 = decide(s_vs, s_hx, (c >> 8) & 0xff, (c >> 16) & 0xff, c >> 24);
+    out[g] = (m0 | (m1 << 8) | (m2 << 16) | (m3 << 24)) ^ inv;
+  }
+  if (first + kFastPxPerThread <= n_px)
+    *reinterpret_cast<uint4*>(mask + first) = make_uint4(out[0], out[1], out[2], out[3]);
+  else
+    for (unsigned long long k = 0; first + k < n_px; k++)
+      mask[first + k] = (uint8_t)(out[k >> 2] >> (8 * (k & 3)));
+}
+
+// device copy of the decision tables for `p`, cached in the context; *out = NULL if `p` cannot be tabulated
+static int flat_tables(pcs_ctx* ctx, const pcs_hsv_params& p, const HsvDecisionTables** out)
+{
+  *out = nullptr;
+  const bool same = ctx->hsv_tables_valid && ctx->hsv_tables_params.h_lo == p.h_lo && ctx->hsv_tables_params.h_hi == p.h_hi &&
+                    ctx->hsv_tables_params.s_lo == p.s_lo && ctx->hsv_tables_params.s_hi == p.s_hi &&
+                    ctx->hsv_tables_params.v_lo == p.v_lo && ctx->hsv_tables_params.v_hi == p.v_hi;
+  if (!same)
+  {
+    static thread_local HsvDecisionTables host;  // must outlive the asynchronous copy below: synchronised before reuse
+    if (ctx->hsv_tables_valid || ctx->hsv_tables_dev)
+      PCS_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (!build_decision_tables(p, host))
+      return PCS_OK;
+    if (!ctx->hsv_tables_dev)
+      PCS_CUDA(cudaMalloc(&ctx->hsv_tables_dev, sizeof(HsvDecisionTables)));
+    PCS_CUDA(cudaMemcpyAsync(ctx->hsv_tables_dev, &host, sizeof(host), cudaMemcpyHostToDevice, ctx->stream));
+    PCS_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->hsv_tables_params = p;
+    ctx->hsv_tables_valid = true;
+  }
+  *out = (const HsvDecisionTables*)ctx->hsv_tables_dev;
+  return PCS_OK;
+}
+
 int launch_hsv_mask(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, int height, size_t stride,
                     const pcs_hsv_params* p, uint8_t* mask_dev, size_t mask_stride, int out_channels)
 {
@@ -171,6 +352,21 @@ int launch_hsv_mask(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, int height,
   dim3 grid((unsigned)((width + kTileW - 1) / kTileW), (unsigned)((height + kTileH - 1) / kTileH));
   dim3 block(kHsvThreads);
   const int inv = p->inverted ? 1 : 0;
+  const bool flat = !p->morph_open && out_channels == 1 && stride == (size_t)width * 3 && mask_stride == (size_t)width &&
+                    (((uintptr_t)bgr_dev | (uintptr_t)mask_dev) & 15u) == 0;
+  if (flat)
+  {
+    const HsvDecisionTables* tables = nullptr;
+    PCS_TRY(flat_tables(ctx, *p, &tables));
+    if (tables)
+    {
+      const unsigned long long n_px = (unsigned long long)width * height;
+      hsv_mask_flat_kernel<<<(unsigned)((n_px + kFastPxPerCta - 1) / kFastPxPerCta), kFastThreads, 0, ctx->stream>>>(
+          bgr_dev, n_px, tables, inv, mask_dev);
+      count_launch(ctx);
+      return check_launch("hsv_mask_flat_kernel");
+    }
+  }
   if (p->morph_open)
   {
     if (out_channels == 1)

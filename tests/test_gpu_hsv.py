@@ -73,3 +73,30 @@ def test_bad_arguments(ctx, pcs):
     assert lib.pcs_hsv_mask(ctx.h, vp, 0, 4, 12, C.byref(p), vp, 4) == pcs.capi.PCS_ERR_BAD_ARG
     assert lib.pcs_hsv_mask(ctx.h, vp, 4, 4, 11, C.byref(p), vp, 4) == pcs.capi.PCS_ERR_BAD_ARG
     assert b"bad argument" in lib.pcs_last_error()
+
+
+@pytest.mark.parametrize("thr", [
+    dict(h_lo=0, h_hi=10, s_lo=0, s_hi=255, v_lo=0, v_hi=255),       # includes hue 0 (both sides of the wrap)
+    dict(h_lo=165, h_hi=179, s_lo=30, s_hi=255, v_lo=10, v_hi=250),   # hues that come from negative numerators
+    dict(h_lo=0, h_hi=179, s_lo=0, s_hi=255, v_lo=0, v_hi=255),       # everything
+    dict(h_lo=100, h_hi=90, s_lo=0, s_hi=255, v_lo=0, v_hi=255),      # empty hue interval
+    dict(h_lo=20, h_hi=160, s_lo=200, s_hi=210, v_lo=77, v_hi=77),    # a single value plane
+    dict(h_lo=-5, h_hi=300, s_lo=-1, s_hi=999, v_lo=-3, v_hi=256),    # bounds outside the representable ranges
+])
+def test_decision_tables_all_colours_custom_thresholds(ctx, pcs, O, thr):
+    """The contiguous fast path folds the thresholds into decision tables; every colour must still agree with the
+    reference arithmetic for arbitrary bounds."""
+    img = all_colours_image()
+    got = ctx.hsv_mask(img, pcs.hsv_params(**thr))
+    want = O.hsv_mask(img, O.default_params(**thr))
+    assert np.array_equal(got, want)
+    inv = ctx.hsv_mask(img[:100], pcs.hsv_params(inverted=1, **thr))
+    assert np.array_equal(inv, 255 - want[:100])
+
+
+@pytest.mark.parametrize("n_px", [1, 15, 16, 17, 4095, 4096, 4097, 100003])
+def test_flat_path_ragged_lengths(ctx, pcs, O, n_px):
+    rng = np.random.default_rng(n_px)
+    img = rng.integers(0, 256, (1, n_px, 3), dtype=np.uint8)
+    img[0, rng.random(n_px) < 0.5] = (140, 90, 50)
+    assert np.array_equal(ctx.hsv_mask(img), O.hsv_mask(img))
