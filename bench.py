@@ -37,7 +37,7 @@ WORKLOADS = {
     # name: (frames per GPU, width, height, resolution, map capacity in voxels)
     "scan300_1280x720_5mm": (300, 1280, 720, 0.005, 1 << 20),
     "frame1_640x480_1cm": (1, 640, 480, 0.01, 1 << 18),
-    "scan16_3840x2160_2mm": (16, 3840, 2160, 0.002, 1 << 23),
+    "scan16_3840x2160_2mm": (16, 3840, 2160, 0.002, 1 << 20),
 }
 DEFAULT_WORKLOAD = "scan300_1280x720_5mm"
 

@@ -133,3 +133,30 @@ def test_empty_mesh_and_bad_mask_type(ctx, pcs):
     ov, of, rgb, flags = ctx.mesh_mask(vmap, verts, faces, pcs.RETURN_OUTSIDE)  # empty map: everything is outside
     assert of.shape[0] == 2 and flags.sum() == 0
     vmap.destroy()
+
+
+def test_python_mirror_of_octomap_mesh_mask(ctx, pcs, O, ref_fixtures, tmp_path):
+    """scan_integration.OctomapMeshMask follows the reference's unit test (octomap_mesh_masking_unit.cpp:45-185)."""
+    from point_cloud_segmentation_b200.scan_integration import OctomapMeshMask, colorPassthrough
+    from util import ramp_cloud
+
+    g = ref_fixtures
+    masker = OctomapMeshMask(ctx)
+    assert masker.getOctree() is None and masker.getInputMesh() is None and masker.getMaskedMesh() is None
+    assert not masker.maskMesh(OctomapMeshMask.MaskType.RETURN_INSIDE)
+    cloud = ramp_cloud(pcs.POINT_DTYPE)
+    masker.setOctree(cloud, 0.1)
+    assert masker.getOctree() is not None
+    assert colorPassthrough(cloud, 25, 100, False, ctx).size == 76
+    vmap, _ = fixture_map(ctx, g)
+    masker.setOctree(vmap)
+    masker.setInputMesh(g["plane_verts"].astype(np.float64), faces4_of(g["plane_faces"]))
+    assert masker.getInputMesh()[0].shape[0] == 6273
+    assert masker.maskMesh(OctomapMeshMask.MaskType.RETURN_COLORIZED) and masker.getMaskedMesh()[1].shape[0] == 12288
+    assert masker.maskMesh(OctomapMeshMask.MaskType.RETURN_OUTSIDE) and masker.getMaskedMesh()[1].shape[0] == 11400
+    path = str(tmp_path / "masked_mesh.ply")
+    assert masker.saveMaskedMesh(path)
+    v, f = O.load_ply_ascii(open(path, "rb").read())
+    assert f.shape[0] == 11400
+    assert masker.maskMesh(1) and not masker.maskMesh(7)  # the action's integers; invalid type -> False
+    vmap.destroy()
