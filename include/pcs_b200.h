@@ -202,6 +202,15 @@ PCS_API int pcs_annotate_frames_dev(pcs_ctx* ctx, pcs_map* map, const pcs_point_
                                     const pcs_annotate_params* params, pcs_point_xyzrgb* annotated_out_dev,
                                     uint8_t* mask_out_dev);
 
+/* The compacted product of stage 2: the labelled points the reference hands to the octree, i.e. what
+ * colorPassthrough(transformPointCloud(annotated frame)) keeps (octomap_mesh_mask_node.cpp:56-68,
+ * octomap_mesh_masking.cpp:110-115) minus the points octomap would silently skip (non-finite, or outside the key range
+ * of `resolution`; pass resolution = 0 to skip the range test).  World-frame coordinates, colour = annotation, input
+ * order preserved (frame-major, row-major).  out == NULL queries the count. */
+PCS_API int pcs_labelled_points(pcs_ctx* ctx, const pcs_point_xyzrgb* clouds, int n_frames, int width, int height,
+                                const float* poses, const pcs_annotate_params* params, double resolution, uint64_t cap,
+                                pcs_point_xyzrgb* out, uint64_t* n_out);
+
 /* ---- stage 3: voxel map (stands in for octomap::OcTree behind tesseract_geometry::Octree) ------------------------- */
 /* A map is a device hash of 48-bit voxel keys (key48 = kz<<32 | ky<<16 | kx, each k = floor(coord / resolution) +
  * 32768 as octomap's coordToKeyChecked) with two hit counters per voxel.  The reference octree for the filter used

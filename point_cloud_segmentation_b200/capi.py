@@ -81,6 +81,7 @@ SIGNATURES = {
     "pcs_transform_cloud": (_i, [_vp, _vp, _vp, _u64, _vp]),
     "pcs_annotate_frames": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, C.POINTER(AnnotateParams), _vp, _vp]),
     "pcs_annotate_frames_dev": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, C.POINTER(AnnotateParams), _vp, _vp]),
+    "pcs_labelled_points": (_i, [_vp, _vp, _i, _i, _i, _vp, C.POINTER(AnnotateParams), _dbl, _u64, _vp, _pu64]),
     "pcs_map_create": (_i, [_vp, _dbl, _u64, _pp]),
     "pcs_map_destroy": (_i, [_vp, _vp]),
     "pcs_map_clear": (_i, [_vp, _vp]),
@@ -445,6 +446,18 @@ class Context:
         _check(self.lib.pcs_annotate_frames(self.h, vmap.h if vmap else None, _p(clouds), n_frames, w, h, _p(posep),
                                             C.byref(p), _p(ann), _p(mask)))
         return ann, mask
+
+    def labelled_points(self, clouds: np.ndarray, n_frames: int, w: int, h: int, poses=None,
+                        params: AnnotateParams | None = None, resolution: float = 0.0) -> np.ndarray:
+        """Order-preserving list of the finite, in-range points whose annotation passes the label filter (world frame)."""
+        clouds = _c(clouds, POINT_DTYPE)
+        p = params or annotate_params()
+        posep = None if poses is None else _c(poses, np.float32).reshape(-1)
+        n = C.c_uint64(0)
+        out = np.empty(max(clouds.size, 1), POINT_DTYPE)
+        _check(self.lib.pcs_labelled_points(self.h, _p(clouds), n_frames, w, h, _p(posep), C.byref(p), float(resolution),
+                                            out.size, _p(out), C.byref(n)))
+        return out[: int(n.value)].copy()
 
     def annotate_frames_dev(self, clouds_dev: int, n_frames: int, w: int, h: int, poses_dev: int | None,
                             params: AnnotateParams, vmap: VoxelMap | None, annotated_dev: int | None,

@@ -316,6 +316,29 @@ struct PassEmit
   }
 };
 
+// labelled-point list: finite after the transform, inside the voxel key range, annotation colour passes the filter
+struct LabelledPred
+{
+  const Point8* pts;  // annotated, world frame
+  double inv_res;     // 0: skip the key-range test
+  int lower, upper, neg;
+  __device__ bool operator()(unsigned long long i) const
+  {
+    const uint4 a = reinterpret_cast<const uint4*>(pts + i)[0];
+    const unsigned int c = reinterpret_cast<const unsigned int*>(pts + i)[4];
+    const float x = __uint_as_float(a.x), y = __uint_as_float(a.y), z = __uint_as_float(a.z);
+    bool ok = finite3(x, y, z) && color_pass((c >> 16) & 0xff, (c >> 8) & 0xff, c & 0xff, lower, upper, neg);
+    if (inv_res > 0.0)
+    {
+      unsigned int k;
+      ok = coord_to_key(inv_res, x, k) && ok;
+      ok = coord_to_key(inv_res, y, k) && ok;
+      ok = coord_to_key(inv_res, z, k) && ok;
+    }
+    return ok;
+  }
+};
+
 static int launch_annotate(pcs_ctx* ctx, pcs_map* map, const Point8* clouds, unsigned int n_frames,
                            unsigned int pts_per_frame, const float* poses, const pcs_annotate_params* prm, Point8* ann,
                            uint8_t* mask, const uint8_t* mask_in)
@@ -639,6 +662,61 @@ int pcs_transform_cloud(pcs_ctx* ctx, const float* pose, const pcs_point_xyzrgb*
   PCS_CUDA(cudaStreamSynchronize(ctx->stream));
   ctx->stats.bytes_h2d += n * 32 + 64;
   ctx->stats.bytes_d2h += n * 32;
+  return PCS_OK;
+}
+
+int pcs_labelled_points(pcs_ctx* ctx, const pcs_point_xyzrgb* clouds, int n_frames, int width, int height,
+                        const float* poses, const pcs_annotate_params* params, double resolution, uint64_t cap,
+                        pcs_point_xyzrgb* out, uint64_t* n_out)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(params && n_out, "NULL argument");
+  PCS_CHECK_ARG(n_frames >= 0 && width > 0 && height > 0, "bad frame shape");
+  PCS_CHECK_ARG(params->lower <= params->upper, "colorPassthrough: lower limit greater than upper limit");
+  PCS_CHECK_ARG(resolution >= 0.0, "resolution must be >= 0");
+  *n_out = 0;
+  const uint64_t n = (uint64_t)n_frames * width * height;
+  if (n == 0)
+    return PCS_OK;
+  PCS_CHECK_ARG(clouds != nullptr, "clouds is NULL");
+  void *d_in = nullptr, *d_ann = nullptr, *d_out = nullptr, *d_pose = nullptr, *scr = nullptr, *h_total = nullptr;
+  PCS_TRY(ctx_staging(ctx, 0, n * 32, &d_in));
+  PCS_TRY(ctx_staging(ctx, 1, n * 32, &d_ann));
+  PCS_TRY(ctx_staging(ctx, 3, n * 32, &d_out));
+  PCS_TRY(ctx_scratch(ctx, compact_scratch_bytes(n), &scr));
+  PCS_TRY(ctx_pinned(ctx, 8, &h_total));
+  PCS_CUDA(cudaMemcpyAsync(d_in, clouds, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+  if (poses)
+  {
+    PCS_TRY(ctx_staging(ctx, 2, (size_t)n_frames * 64, &d_pose));
+    PCS_CUDA(cudaMemcpyAsync(d_pose, poses, (size_t)n_frames * 64, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  // pass 1: detector + labelling + transform (world-frame annotated cloud); pass 2: ballot compaction of the survivors
+  pcs_annotate_params prm = *params;
+  prm.world_frame_output = 1;
+  PCS_TRY(annotate_dev(ctx, nullptr, (const pcs_point_xyzrgb*)d_in, n_frames, width, height, (const float*)d_pose, &prm,
+                       (pcs_point_xyzrgb*)d_ann, nullptr));
+  LabelledPred pred{ (const Point8*)d_ann, resolution > 0.0 ? 1.0 / resolution : 0.0, params->lower, params->upper,
+                     params->limit_negative ? 1 : 0 };
+  PassEmit emit{ (const Point8*)d_ann, (Point8*)d_out };
+  const unsigned long long* d_total = nullptr;
+  PCS_TRY(compact_run(ctx, pred, emit, n, scr, &d_total));
+  PCS_CUDA(cudaMemcpyAsync(h_total, d_total, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  PCS_CUDA(cudaStreamSynchronize(ctx->stream));
+  const uint64_t m = *(const unsigned long long*)h_total;
+  *n_out = m;
+  ctx->stats.bytes_h2d += n * 32;
+  if (!out)
+    return PCS_OK;  // count query
+  if (m > cap)
+  {
+    set_error("output holds %llu points, %llu labelled points found", (unsigned long long)cap, (unsigned long long)m);
+    return PCS_ERR_CAPACITY;
+  }
+  if (m)
+    PCS_CUDA(cudaMemcpyAsync(out, d_out, m * 32, cudaMemcpyDeviceToHost, ctx->stream));
+  PCS_CUDA(cudaStreamSynchronize(ctx->stream));
+  ctx->stats.bytes_d2h += m * 32 + 8;
   return PCS_OK;
 }
 

@@ -161,3 +161,32 @@ def test_accumulation_is_order_and_batching_independent(ctx, pcs, O):
     assert a.size() == (0, 0) and a.export()[0].size == 0
     a.destroy()
     b.destroy()
+
+
+@pytest.mark.parametrize("flt", [(255, 255, False), (0, 0, False), (0, 255, False), (10, 200, True)])
+def test_labelled_points_compaction(ctx, pcs, O, flt):
+    """Stage 2's compacted product: colorPassthrough(transform(annotated frame)) without the points octomap skips, in
+    input order, byte for byte."""
+    import ctypes as C
+
+    lower, upper, neg = flt
+    w, h, n_frames, res = 150, 90, 3, 0.005
+    frames, poses = make_scan(O, n_frames, w, h, first=7)
+    frames["x"][::97] = 400.0  # outside the +-163.84 m key range at 5 mm
+    frames["y"][5::131] = np.inf
+    want = []
+    inv = 1.0 / res
+    for f in range(n_frames):
+        ann, _ = O.annotate_frame(frames[f * w * h:(f + 1) * w * h], w, h)
+        world = O.transform_points(poses[f], ann)
+        kept = O.color_passthrough(world, lower, upper, neg)
+        k = C.c_uint16(0)
+        ok = np.array([all(O.lib().orc_coord_to_key(inv, float(p[a]), C.byref(k)) for a in ("x", "y", "z")) for p in kept], bool)
+        want.append(kept[ok] if kept.size else kept)
+    want = np.concatenate(want)
+    got = ctx.labelled_points(frames, n_frames, w, h, poses, pcs.annotate_params(lower=lower, upper=upper, limit_negative=neg), res)
+    assert same_bytes(got, want)
+    assert 0 < got.size < frames.size
+    # without the range test only non-finite points are culled
+    got2 = ctx.labelled_points(frames, n_frames, w, h, poses, pcs.annotate_params(lower=lower, upper=upper, limit_negative=neg), 0.0)
+    assert got2.size >= got.size and np.isfinite(got2["x"]).all()
