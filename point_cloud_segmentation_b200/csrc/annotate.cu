@@ -43,7 +43,7 @@ constexpr int kAnnThreads = PCS_ANN_THREADS;
 constexpr int kAnnRoundUnroll = PCS_ANN_ROUND_UNROLL;
 constexpr int kAnnUnroll = PCS_ANN_UNROLL;            // points in flight per thread
 constexpr int kAnnRounds = PCS_ANN_ROUNDS;            // rounds per tile
-constexpr int kAnnTile = kAnnThreads * kAnnUnroll * kAnnRounds;  // 2048 points: one pose / frame lookup per tile
+constexpr int kAnnTile = kAnnThreads * kAnnUnroll * kAnnRounds;  // 1024 points: one pose / frame lookup per tile
 
 struct AnnotateArgs
 {

@@ -9,7 +9,6 @@
 
 namespace pcs
 {
-constexpr int kNumSMs = 148;  // B200: 2 dies x 74 SMs; grids are sized in multiples of this
 constexpr int kCopyStreams = 2;
 
 void set_error(const char* fmt, ...);
