@@ -4,6 +4,7 @@
 #include <pcs_detection/hsv_thresholding.h>
 #include <pcs_detection/point_cloud_annotator.h>
 #include <pcs_detection/utils.h>
+#include <pcs_ros/point_cloud_annotator_node.h>
 
 #include "mini_test.h"
 
@@ -175,6 +176,44 @@ TEST(PointCloudAnnotatorUnit, fusedModeEqualsCallbackMode)
       detected += p.r == 255;
     EXPECT_TRUE(detected > 500 && detected < 2500);
   }
+}
+
+TEST(PointCloudAnnotatorNodeUnit, toggleAndPublish)
+{
+  // pcs_ros/src/point_cloud_annotator_node.cpp:57-61,106-115,157-163 without ROS
+  auto cloud = rampCloud();
+  cloud->width = 51;
+  cloud->height = 5;  // 255 points as a 51 x 5 organized cloud
+  for (size_t i = 0; i < cloud->points.size(); ++i)
+    if (i % 3 == 0)
+    {
+      cloud->points[i].b = 140;
+      cloud->points[i].g = 90;
+      cloud->points[i].r = 50;
+    }
+  int published = 0, debug_images = 0, detected = 0;
+  pcs_ros::PointCloudAnnotatorNode node([&](PointCloud<PointXYZRGB>::ConstPtr c) {
+    published++;
+    detected = 0;
+    for (const PointXYZRGB& p : c->points)
+      detected += p.r == 255 && p.g == 255 && p.b == 255;
+  });
+  node.setDebugImageSink([&](const Mat&) { debug_images++; });
+  node.subscriberCallback(cloud);
+  EXPECT_EQ(published, 1);
+  EXPECT_EQ(debug_images, 1);
+  EXPECT_EQ(detected, 85);
+  EXPECT_TRUE(node.toggleAnnotation(false) == "Annotation disabled");
+  node.subscriberCallback(cloud);
+  EXPECT_EQ(published, 1);  // dropped while disabled
+  EXPECT_TRUE(node.toggleAnnotation(true) == "Annotation enabled");
+  pcs_annotate_params prm;
+  pcs_annotate_default_params(&prm);
+  node.setFusedHsvDetector(prm);
+  node.subscriberCallback(cloud);
+  EXPECT_EQ(published, 2);
+  EXPECT_EQ(debug_images, 1);  // the fused path never materialises the 2D annotation
+  EXPECT_EQ(detected, 85);
 }
 
 int main() { return mini_test::run_all(); }
