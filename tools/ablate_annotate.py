@@ -5,14 +5,14 @@ import numpy as np
 import bench
 import point_cloud_segmentation_b200 as pcs
 
-n, w, h = 300, 1280, 720
+n, w, h, res = (16, 3840, 2160, 0.002) if len(sys.argv) > 1 and sys.argv[1] == '4k' else (300, 1280, 720, 0.005)
 ctx = pcs.Context(0)
 poses = np.stack([bench.synth_pose(f) for f in range(n)])
 d_pose = ctx.dev_alloc(poses.nbytes); ctx.h2d(d_pose, poses)
 npts = n * w * h
 d_in, d_ann, d_mask = ctx.dev_alloc(npts * 32), ctx.dev_alloc(npts * 32), ctx.dev_alloc(npts)
 ctx.synth_frames_dev(bench.SEED, 0, n, w, h, d_pose, d_in)
-vmap = ctx.create_map(0.005, 1 << 21)
+vmap = ctx.create_map(res, 1 << 20)
 prm = pcs.annotate_params(lower=255, upper=255)
 e0, e1 = ctx.event(), ctx.event()
 for name, m, a, k, bpp in [("map+ann+mask", vmap, d_ann, d_mask, 65), ("ann+mask", None, d_ann, d_mask, 65), ("map+ann", vmap, d_ann, None, 64),
