@@ -188,24 +188,30 @@ __global__ void __launch_bounds__(256, 4) mesh_vertex_probe_kernel(MapView m, do
   if (ok)
   {
     const int idx[3] = { f.y, f.z, f.w };
+    double v[3][3];
     bool finite = true;
 #pragma unroll
     for (int i = 0; i < 3; i++)
+#pragma unroll
+      for (int a = 0; a < 3; a++)
+      {
+        v[i][a] = __ldg(verts + 3ull * idx[i] + a);
+        finite = finite && isfinite(v[i][a]);
+      }
+    // one vertex after the other, stopping at the first hit (for a mesh finer than the voxels that is vertex 0)
+    for (int i = 0; i < 3 && !flag; i++)
     {
-      double v[3];
-      int k[3];
+      unsigned long long key = 0;
       bool inside = true;
 #pragma unroll
       for (int a = 0; a < 3; a++)
       {
-        v[a] = __ldg(verts + 3ull * idx[i] + a);
-        finite = finite && isfinite(v[a]);
-        const double e = fmin(fmax(floor(v[a] * m.inv_res), -32768.0), 32767.0);
-        k[a] = (int)e + 32768;
-        inside = inside && v[a] >= vox_lo(k[a], res) && v[a] <= vox_hi(k[a], res);  // exact test guards the estimate
+        // e is integral, so e * res and (e + 1) * res are exactly the voxel's bounds (k - 32768) * res, (k - 32767) * res
+        const double e = fmin(fmax(floor(v[i][a] * m.inv_res), -32768.0), 32767.0);
+        inside = inside && v[i][a] >= e * res && v[i][a] <= (e + 1.0) * res;  // exact test guards the estimate
+        key |= (unsigned long long)((int)e + 32768) << (16 * a);
       }
-      if (!flag && inside &&
-          map_occupied(m, ((unsigned long long)k[2] << 32) | ((unsigned long long)k[1] << 16) | (unsigned long long)k[0]))
+      if (inside && map_occupied(m, key))
         flag = 1;
     }
     if (!finite)
