@@ -163,7 +163,7 @@ PCS_API int pcs_color_passthrough(pcs_ctx* ctx, const pcs_point_xyzrgb* in, uint
 /* No counterpart in the reference.  Same filter as pcs_color_passthrough, for hosts that must not let the library
  * allocate: a per-frame callback where cudaMalloc / cudaFree would stall every stream on the device, or a GPU shared
  * with a process that reserved nearly all device memory at start-up, where a late allocation can fail.  The call
- * allocates nothing (no cudaMalloc / cudaFree, no library scratch growth):
+ * itself allocates nothing (no cudaMalloc / cudaFree, no library scratch growth):
  *   - in_dev, out_dev (room for n points) and n_out_dev (one uint64_t) are DEVICE pointers owned by the caller; the
  *     work is enqueued on the context's stream and the count stays on the device;
  *   - the per-block counts and offsets of the compaction live in a fixed 48.25 KiB array inside the library image,
@@ -171,8 +171,11 @@ PCS_API int pcs_color_passthrough(pcs_ctx* ctx, const pcs_point_xyzrgb* in, uint
  *   - n may not exceed PCS_NOALLOC_MAX_POINTS (one 3840x2160 frame fits); more returns PCS_ERR_CAPACITY;
  *   - all calls on a device share that array and it keeps the previous call's contents (nothing in it needs to start
  *     at zero); calls whose kernels overlap on the GPU race on it, so keep them ordered;
- *   - the first call on a device looks up the array's device address once: make that first call before starting any
- *     stream capture. */
+ *   - in_dev and out_dev must be distinct, non-overlapping ranges (the filter cannot run in place; an overlap is
+ *     refused with PCS_ERR_BAD_ARG); n_out_dev must be 8-byte aligned;
+ *   - the first call on a device looks up the array's device address once, and with CUDA's lazy module loading it is
+ *     also the call at which the driver loads the library's device code (the only point where memory may be reserved on
+ *     the caller's behalf): make that first call early, before the time-critical phase and before any stream capture. */
 #define PCS_NOALLOC_MAX_POINTS (1ull << 23)
 PCS_API int pcs_color_passthrough_noalloc_dev(pcs_ctx* ctx, const pcs_point_xyzrgb* in_dev, uint64_t n, int lower,
                                               int upper, int limit_negative, pcs_point_xyzrgb* out_dev,
@@ -215,7 +218,13 @@ PCS_API int pcs_labelled_points(pcs_ctx* ctx, const pcs_point_xyzrgb* clouds, in
 /* A map is a device hash of 48-bit voxel keys (key48 = kz<<32 | ky<<16 | kx, each k = floor(coord / resolution) +
  * 32768 as octomap's coordToKeyChecked) with two hit counters per voxel.  The reference octree for the filter used
  * at integration time is exactly { key : count1 >= 1 } with log-odds LUT[min(count1, 5)]
- * (octomap hit = logodds(0.7), clamp logodds(0.971)).  `capacity_voxels` bounds the number of distinct voxels. */
+ * (octomap hit = logodds(0.7), clamp logodds(0.971)).  `capacity_voxels` bounds the number of distinct voxels: the table
+ * has at least 2 x capacity_voxels slots, and pcs_map_size / pcs_map_export report PCS_ERR_CAPACITY as soon as more than
+ * capacity_voxels distinct voxels have been inserted (results stay exact up to the slot count, but buffers sized from
+ * capacity_voxels would no longer fit).
+ * Limit: the two counters of a voxel are the halves of ONE 64-bit word updated by a single atomic add, so count0 is exact
+ * only below 2^32 rejected points per voxel -- at 2^32 it would carry into count1.  A voxel of the BASELINE scans sees
+ * ~10^4 points; a long-lived accumulating map must be exported and cleared before any voxel can reach 4.29e9 points. */
 PCS_API int pcs_map_create(pcs_ctx* ctx, double resolution, uint64_t capacity_voxels, pcs_map** map);
 PCS_API int pcs_map_destroy(pcs_ctx* ctx, pcs_map* map);
 PCS_API int pcs_map_clear(pcs_ctx* ctx, pcs_map* map);

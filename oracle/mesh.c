@@ -217,6 +217,14 @@ static int key_range(double tmin, double tmax, double res, double inv, int* klo,
 {
   if (!isfinite(tmin) || !isfinite(tmax))
     return 0;
+  /* clamp to the key range first: the correction loops then run a bounded number of steps for any finite vertex */
+  const double range_lo = vox_lo(0, res), range_hi = vox_hi(65535, res);
+  if (tmin > range_hi || tmax < range_lo)
+    return 0;
+  if (tmin < range_lo)
+    tmin = range_lo;
+  if (tmax > range_hi)
+    tmax = range_hi;
   double e = floor(tmin * inv);
   if (e < -40000.0)
     e = -40000.0;

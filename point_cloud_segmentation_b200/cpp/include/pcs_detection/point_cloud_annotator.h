@@ -67,6 +67,14 @@ public:
     auto image_2d = std::make_shared<Mat>();
     if (!fused_)
       cloudToImage(input_cloud, *position_image, *image_2d);
+    else if (!input_cloud || (input_cloud->width == 1 && input_cloud->height == 1) ||
+             input_cloud->points.size() != static_cast<std::size_t>(input_cloud->width) * input_cloud->height)
+    {
+      // the fused path skips cloudToImage and with it the reference's organized-cloud check (utils.h:103-105); the
+      // kernel reads width * height points per frame, so anything else is refused here instead of asserted there
+      pcs_compat::logError("addPointCloud: cloud is not organized (width * height != points.size(), or 1 x 1)");
+      return false;
+    }
     PointCloudData data(input_cloud, position_image, image_2d);
     {
       std::lock_guard<std::mutex> lock(buffer_mutex_);
@@ -139,15 +147,19 @@ protected:
 
   bool annotateFused()
   {
+    // the batch stays queued until every call has succeeded; on failure only the front entry is dropped, which is what
+    // the reference does when the detector callback fails (point_cloud_annotator.cpp:51-56)
     std::vector<PointCloudData> batch;
     {
       std::lock_guard<std::mutex> lock(buffer_mutex_);
       for (std::size_t idx = 0; idx < batch_size_; idx++)
-      {
-        batch.push_back(input_buffer_.front());
-        input_buffer_.pop_front();
-      }
+        batch.push_back(input_buffer_[idx]);
     }
+    auto drop = [this](std::size_t n) {
+      std::lock_guard<std::mutex> lock(buffer_mutex_);
+      for (std::size_t idx = 0; idx < n && !input_buffer_.empty(); idx++)
+        input_buffer_.pop_front();
+    };
     pointCloudVec results(batch_size_);
     // frames of one shape go through one call; a batch of mixed shapes falls back to one call per frame
     std::size_t i = 0;
@@ -167,6 +179,7 @@ protected:
       if (rc != PCS_OK)
       {
         pcs_compat::logError(pcs_last_error());
+        drop(1);
         return false;
       }
       for (std::size_t f = 0; f < nf; f++)
@@ -181,6 +194,7 @@ protected:
       }
       i = j;
     }
+    drop(batch_size_);
     return deliver(results);
   }
 

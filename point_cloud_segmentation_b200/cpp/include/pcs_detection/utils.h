@@ -6,6 +6,7 @@
 #define PCS_DETECTION_UTILS_H
 
 #include <limits>
+#include <stdexcept>
 #include <string>
 
 #include "pcs_compat/types.h"
@@ -31,6 +32,41 @@ inline std::string type2str(const int type)
     default:
       return "UserC1";
   }
+}
+
+/** @brief masked_image = input_image.mul(mask): per-element product, saturated to the element type (reference :82-86).
+ * Host-side helper exactly as in the reference (nothing on the hot path calls it); both images must have the same size
+ * and type, as cv::Mat::mul requires (it throws otherwise, so does this). */
+inline bool applyMask(const Mat& input_image, const Mat& mask, Mat& masked_image)
+{
+  if (input_image.rows != mask.rows || input_image.cols != mask.cols || input_image.type() != mask.type())
+    throw std::invalid_argument("applyMask: size or type mismatch (cv::Mat::mul)");
+  Mat out(input_image.rows, input_image.cols, input_image.type());
+  const std::size_t row_elems = static_cast<std::size_t>(input_image.cols) * (input_image.type() == pcs_compat::CV_8UC1 ? 1 : 3);
+  for (int r = 0; r < input_image.rows; r++)
+  {
+    if (input_image.type() == pcs_compat::CV_64FC3)
+    {
+      const double* a = reinterpret_cast<const double*>(input_image.data + input_image.step * static_cast<std::size_t>(r));
+      const double* b = reinterpret_cast<const double*>(mask.data + mask.step * static_cast<std::size_t>(r));
+      double* o = reinterpret_cast<double*>(out.data + out.step * static_cast<std::size_t>(r));
+      for (std::size_t i = 0; i < row_elems; i++)
+        o[i] = a[i] * b[i];
+    }
+    else
+    {
+      const uint8_t* a = input_image.data + input_image.step * static_cast<std::size_t>(r);
+      const uint8_t* b = mask.data + mask.step * static_cast<std::size_t>(r);
+      uint8_t* o = out.data + out.step * static_cast<std::size_t>(r);
+      for (std::size_t i = 0; i < row_elems; i++)
+      {
+        const unsigned v = static_cast<unsigned>(a[i]) * b[i];
+        o[i] = static_cast<uint8_t>(v > 255u ? 255u : v);  // cv::saturate_cast<uchar>
+      }
+    }
+  }
+  masked_image = out;
+  return true;
 }
 
 /** @brief Organized XYZRGB cloud -> 64FC3 position image + 8UC3 BGR image (reference :98-129). */

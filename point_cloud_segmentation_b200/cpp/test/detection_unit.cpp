@@ -178,6 +178,51 @@ TEST(PointCloudAnnotatorUnit, fusedModeEqualsCallbackMode)
   }
 }
 
+TEST(PointCloudAnnotatorUnit, fusedModeRefusesUnorganizedClouds)
+{
+  // the fused path skips cloudToImage, so its organized-cloud check (utils.h:103-105) is made at addPointCloud
+  PointCloudAnnotator fast(&ImageAnnotatorCallback_Throw, &ResultsCallback_Keep, 1);
+  pcs_annotate_params prm;
+  pcs_annotate_default_params(&prm);
+  fast.useFusedHsvDetector(prm);
+  PointCloud<PointXYZRGB>::Ptr bad(new PointCloud<PointXYZRGB>());
+  bad->width = 64;
+  bad->height = 48;
+  bad->points.resize(100);  // width * height != points.size()
+  EXPECT_FALSE(fast.addPointCloud(bad));
+  PointCloud<PointXYZRGB>::Ptr one(new PointCloud<PointXYZRGB>());
+  one->width = 1;
+  one->height = 1;
+  one->points.resize(1);
+  EXPECT_FALSE(fast.addPointCloud(one));
+  g_last.clear();
+  PointCloud<PointXYZRGB>::Ptr ok(new PointCloud<PointXYZRGB>());
+  ok->width = 8;
+  ok->height = 4;
+  ok->points.resize(32);
+  EXPECT_TRUE(fast.addPointCloud(ok));  // the refused clouds were never queued
+  EXPECT_EQ(g_last.size(), 1u);
+}
+
+TEST(UtilsUnit, applyMask)
+{
+  // utils.h:82-86: input.mul(mask), saturated
+  Mat img(2, 3, pcs_compat::CV_8UC3), mask(2, 3, pcs_compat::CV_8UC3), out;
+  for (int i = 0; i < 18; i++)
+  {
+    img.data[i] = static_cast<uint8_t>(10 * i);
+    mask.data[i] = static_cast<uint8_t>(i % 3);  // 0, 1, 2
+  }
+  EXPECT_TRUE(pcs_detection::applyMask(img, mask, out));
+  EXPECT_EQ(out.rows, 2);
+  EXPECT_EQ(out.cols, 3);
+  for (int i = 0; i < 18; i++)
+  {
+    const unsigned v = 10u * i * (i % 3);
+    EXPECT_EQ(static_cast<unsigned>(out.data[i]), v > 255u ? 255u : v);
+  }
+}
+
 TEST(PointCloudAnnotatorNodeUnit, toggleAndPublish)
 {
   // pcs_ros/src/point_cloud_annotator_node.cpp:57-61,106-115,157-163 without ROS

@@ -14,13 +14,11 @@
 // is touched through warp-aggregated 64-bit atomics (one per distinct voxel per warp).
 #include "common.cuh"
 #include "compact.cuh"
+#include "annotate.cuh"
 #include "hsv.cuh"
 
 namespace pcs
 {
-int launch_hsv_mask(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, int height, size_t stride,
-                    const pcs_hsv_params* p, uint8_t* mask_dev, size_t mask_stride, int out_channels);
-
 #ifndef PCS_ANN_UNROLL
 #define PCS_ANN_UNROLL 1
 #endif
@@ -45,83 +43,7 @@ constexpr int kAnnUnroll = PCS_ANN_UNROLL;            // points in flight per th
 constexpr int kAnnRounds = PCS_ANN_ROUNDS;            // rounds per tile
 constexpr int kAnnTile = kAnnThreads * kAnnUnroll * kAnnRounds;  // 1024 points: one pose / frame lookup per tile
 
-struct AnnotateArgs
-{
-  const Point8* cloud;
-  Point8* ann;
-  uint8_t* mask;
-  const uint8_t* mask_in;  // precomputed detector output (opening enabled), else NULL
-  const float* poses;      // n_frames x 16 row-major, or NULL
-  unsigned int pts_per_frame;
-  unsigned int tiles_per_frame;
-  unsigned int n_tiles;
-  HsvBounds hsv;
-  int inverted;
-  int pass_black, pass_white;  // colorPassthrough of the two annotation colours
-  int world_out;
-  MapView map;
-};
-
-struct Pose
-{
-  float m[12];
-};
-
-// everything that happens to one point once its 32 bytes have arrived
-template <bool HAS_MAP, bool WRITE_ANN, bool WRITE_MASK, bool MASK_IN>
-__device__ __forceinline__ void annotate_point(const AnnotateArgs& a, const int* __restrict__ s_lut, const Pose& P,
-                                               const bool has_pose, const Point8& p, const unsigned long long idx,
-                                               const bool in_frame)
-{
-  bool det;
-  if (MASK_IN)
-    det = in_frame && a.mask_in[idx] != 0;
-  else
-  {
-    const int b = p.rgba & 0xff, g = (p.rgba >> 8) & 0xff, r = (p.rgba >> 16) & 0xff;
-    det = hsv_in_range(s_lut, b, g, r, a.hsv) != (a.inverted != 0);
-  }
-  const float x = p.x, y = p.y, z = p.z;
-  float wx = x, wy = y, wz = z;
-  if (has_pose && (HAS_MAP || WRITE_ANN))
-  {
-    // non-finite inputs come out non-finite in every component (NaN * 0 = NaN), so no test is needed before
-    wx = xform_row(P.m[0], P.m[1], P.m[2], P.m[3], x, y, z);
-    wy = xform_row(P.m[4], P.m[5], P.m[6], P.m[7], x, y, z);
-    wz = xform_row(P.m[8], P.m[9], P.m[10], P.m[11], x, y, z);
-  }
-  if (in_frame)
-  {
-    if (WRITE_MASK && !MASK_IN)
-      a.mask[idx] = det ? 255 : 0;
-    if (WRITE_ANN)
-    {
-      Point8 o;
-      // pcl::transformPointCloud leaves non-finite points untouched
-      const bool w = a.world_out != 0 && finite3(x, y, z);
-      o.x = w ? wx : x;
-      o.y = w ? wy : y;
-      o.z = w ? wz : z;
-      o.w = 1.0f;                       // pcl::PointXYZRGB() sets data[3] = 1
-      o.rgba = det ? 0x00ffffffu : 0u;  // r = g = b = mask, alpha 0 (utils.h:161-162)
-      o.p0 = o.p1 = o.p2 = 0u;
-      st_point_stream(a.ann + idx, o);
-    }
-  }
-  if (HAS_MAP)
-  {
-    unsigned int kx, ky, kz;
-    bool valid = in_frame && finite3(wx, wy, wz);
-    valid = coord_to_key(a.map.inv_res, wx, kx) && valid;
-    valid = coord_to_key(a.map.inv_res, wy, ky) && valid;
-    valid = coord_to_key(a.map.inv_res, wz, kz) && valid;
-    const unsigned long long key = ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | kx;
-    const bool cls1 = det ? (a.pass_white != 0) : (a.pass_black != 0);
-    map_add_warp(a.map, valid, key, cls1);
-  }
-}
-
-template <bool HAS_MAP, bool WRITE_ANN, bool WRITE_MASK, bool MASK_IN>
+template <bool HAS_MAP, bool WRITE_ANN, bool WRITE_MASK>
 __global__ void __launch_bounds__(kAnnThreads, PCS_ANN_MIN_BLOCKS) annotate_kernel(const AnnotateArgs a)
 {
   __shared__ int s_lut[512];
@@ -164,8 +86,7 @@ __global__ void __launch_bounds__(kAnnThreads, PCS_ANN_MIN_BLOCKS) annotate_kern
     if (!lut_ready)
     {
       // the detector's tables (2 KB, L2-resident) are fetched while the first points are already in flight
-      if (!MASK_IN)
-        load_hsv_lut(s_lut);
+      load_hsv_lut(s_lut);
       __syncthreads();
       lut_ready = true;
     }
@@ -184,8 +105,7 @@ __global__ void __launch_bounds__(kAnnThreads, PCS_ANN_MIN_BLOCKS) annotate_kern
       for (int u = 0; u < kAnnUnroll; u++)
       {
         const unsigned int l = local + u * kAnnThreads;
-        annotate_point<HAS_MAP, WRITE_ANN, WRITE_MASK, MASK_IN>(a, s_lut, P, has_pose, cur[u], frame_base + l,
-                                                                l < a.pts_per_frame);
+        annotate_point<HAS_MAP, WRITE_ANN, WRITE_MASK>(a, s_lut, P, has_pose, cur[u], frame_base + l, l < a.pts_per_frame);
       }
 #pragma unroll
       for (int u = 0; u < kAnnUnroll; u++)
@@ -339,17 +259,17 @@ struct LabelledPred
   }
 };
 
-static int launch_annotate(pcs_ctx* ctx, pcs_map* map, const Point8* clouds, unsigned int n_frames,
-                           unsigned int pts_per_frame, const float* poses, const pcs_annotate_params* prm, Point8* ann,
-                           uint8_t* mask, const uint8_t* mask_in)
+int fill_annotate_args(pcs_map* map, const Point8* clouds, unsigned int n_frames, unsigned int width, unsigned int height,
+                       const float* poses, const pcs_annotate_params* prm, Point8* ann, uint8_t* mask, AnnotateArgs& a)
 {
-  AnnotateArgs a;
+  const unsigned int pts_per_frame = width * height;
   a.cloud = clouds;
   a.ann = ann;
   a.mask = mask;
-  a.mask_in = mask_in;
   a.poses = poses;
   a.pts_per_frame = pts_per_frame;
+  a.width = width;
+  a.height = height;
   a.tiles_per_frame = (pts_per_frame + kAnnTile - 1) / kAnnTile;
   if ((unsigned long long)a.tiles_per_frame * n_frames > 0x7fffffffull)
   {
@@ -359,6 +279,7 @@ static int launch_annotate(pcs_ctx* ctx, pcs_map* map, const Point8* clouds, uns
   }
   a.n_tiles = a.tiles_per_frame * n_frames;
   a.hsv = HsvBounds{ prm->hsv.h_lo, prm->hsv.h_hi, prm->hsv.s_lo, prm->hsv.s_hi, prm->hsv.v_lo, prm->hsv.v_hi };
+  a.hsv_tables = nullptr;
   a.inverted = prm->hsv.inverted ? 1 : 0;
   // colorPassthrough on the annotation colours (0,0,0) and (255,255,255), octomap_mesh_masking.cpp:75-87
   const int lo = prm->lower, up = prm->upper;
@@ -369,74 +290,58 @@ static int launch_annotate(pcs_ctx* ctx, pcs_map* map, const Point8* clouds, uns
     a.map = map->view;
   else
     a.map = MapView{ nullptr, 0, nullptr, nullptr, 0.0 };
+  return PCS_OK;
+}
 
+static int launch_annotate(pcs_ctx* ctx, const AnnotateArgs& a, bool hm, bool wa, bool wm)
+{
 #if PCS_ANN_PERSISTENT
   const unsigned int max_blocks = (unsigned int)ctx->sm_count * (unsigned int)PCS_ANN_MIN_BLOCKS;  // one resident wave
   const unsigned int grid = a.n_tiles < max_blocks ? a.n_tiles : max_blocks;
 #else
-  const unsigned int grid = a.n_tiles;  // one 2048-point tile per CTA
+  const unsigned int grid = a.n_tiles;  // one 1024-point tile per CTA
 #endif
-  if (grid == 0)
-    return PCS_OK;
-  const bool hm = map != nullptr, wa = ann != nullptr, wm = mask != nullptr && mask_in == nullptr, mi = mask_in != nullptr;
-  if (!hm && !wa && !wm)
-    return PCS_OK;  // nothing to produce (the detector pass, if any, already wrote the mask)
-#define PCS_ANN_CASE(HM, WA, WM, MI)                                                                                   \
-  if (hm == HM && wa == WA && wm == WM && mi == MI)                                                                    \
-    annotate_kernel<HM, WA, WM, MI><<<grid, kAnnThreads, 0, ctx->stream>>>(a);
-  PCS_ANN_CASE(true, true, true, false)
-  PCS_ANN_CASE(true, true, false, false)
-  PCS_ANN_CASE(true, false, true, false)
-  PCS_ANN_CASE(true, false, false, false)
-  PCS_ANN_CASE(false, true, true, false)
-  PCS_ANN_CASE(false, true, false, false)
-  PCS_ANN_CASE(false, false, true, false)
-  PCS_ANN_CASE(true, true, false, true)
-  PCS_ANN_CASE(true, false, false, true)
-  PCS_ANN_CASE(false, true, false, true)
+#define PCS_ANN_CASE(HM, WA, WM)                                                                                       \
+  if (hm == HM && wa == WA && wm == WM)                                                                                \
+    annotate_kernel<HM, WA, WM><<<grid, kAnnThreads, 0, ctx->stream>>>(a);
+  PCS_ANN_CASE(true, true, true)
+  PCS_ANN_CASE(true, true, false)
+  PCS_ANN_CASE(true, false, true)
+  PCS_ANN_CASE(true, false, false)
+  PCS_ANN_CASE(false, true, true)
+  PCS_ANN_CASE(false, true, false)
+  PCS_ANN_CASE(false, false, true)
 #undef PCS_ANN_CASE
   count_launch(ctx);
   return check_launch("annotate_kernel");
 }
 
-// detector with the opening enabled: BGR plane extracted from the clouds, image kernel per frame -> mask buffer
-static int detector_pass(pcs_ctx* ctx, const Point8* clouds, int n_frames, int width, int height,
-                         const pcs_hsv_params* hsv, uint8_t* bgr_tmp, uint8_t* mask)
-{
-  const unsigned long long n = (unsigned long long)n_frames * width * height;
-  cloud_to_image_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, ctx->stream>>>(clouds, n, nullptr, bgr_tmp);
-  count_launch(ctx);
-  PCS_TRY(check_launch("cloud_to_image_kernel"));
-  for (int f = 0; f < n_frames; f++)
-  {
-    const size_t off = (size_t)f * width * height;
-    PCS_TRY(launch_hsv_mask(ctx, bgr_tmp + 3 * off, width, height, (size_t)width * 3, hsv, mask + off, (size_t)width, 1));
-  }
-  return PCS_OK;
-}
-
+// One launch for the whole batch, with or without the opening: the detector runs inside the kernel either way (no BGR
+// plane, no mask image and no per-frame launch).
 int annotate_dev(pcs_ctx* ctx, pcs_map* map, const pcs_point_xyzrgb* clouds, int n_frames, int width, int height,
                  const float* poses, const pcs_annotate_params* prm, pcs_point_xyzrgb* ann, uint8_t* mask)
 {
   const unsigned long long ppf = (unsigned long long)width * height;
-  const uint8_t* mask_in = nullptr;
+  const bool hm = map != nullptr, wa = ann != nullptr, wm = mask != nullptr;
+  if (!hm && !wa && !wm)
+    return PCS_OK;  // nothing to produce
+  AnnotateArgs a;
+  PCS_TRY(fill_annotate_args(map, (const Point8*)clouds, (unsigned int)n_frames, (unsigned int)width, (unsigned int)height,
+                             poses, prm, (Point8*)ann, mask, a));
+  ctx->stats.points_in += ppf * n_frames;
+  if (a.n_tiles == 0)
+    return PCS_OK;
   if (prm->hsv.morph_open)
   {
-    void* bgr_tmp = nullptr;
-    uint8_t* mbuf = mask;
-    PCS_TRY(ctx_staging(ctx, 6, (size_t)(ppf * n_frames * 3), &bgr_tmp));
-    if (!mbuf)
+    PCS_TRY(hsv_decision_tables(ctx, prm->hsv, &a.hsv_tables));
+    if (!a.hsv_tables)
     {
-      void* t = nullptr;
-      PCS_TRY(ctx_staging(ctx, 7, (size_t)(ppf * n_frames), &t));
-      mbuf = (uint8_t*)t;
+      set_error("HSV thresholds cannot be tabulated");  // cannot happen for interval bounds; kept as a guard
+      return PCS_ERR_BAD_ARG;
     }
-    PCS_TRY(detector_pass(ctx, (const Point8*)clouds, n_frames, width, height, &prm->hsv, (uint8_t*)bgr_tmp, mbuf));
-    mask_in = mbuf;
+    return launch_annotate_open(ctx, a, (unsigned int)n_frames, hm, wa, wm);
   }
-  ctx->stats.points_in += ppf * n_frames;
-  return launch_annotate(ctx, map, (const Point8*)clouds, (unsigned int)n_frames, (unsigned int)ppf, poses, prm,
-                         (Point8*)ann, mask, mask_in);
+  return launch_annotate(ctx, a, hm, wa, wm);
 }
 }  // namespace pcs
 
@@ -501,47 +406,53 @@ int pcs_annotate_frames(pcs_ctx* ctx, pcs_map* map, const pcs_point_xyzrgb* clou
     PCS_CUDA(cudaMemcpyAsync(d_pose, poses, (size_t)n_frames * 16 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     ctx->stats.bytes_h2d += (size_t)n_frames * 64;
   }
-  cudaEvent_t ev_in[2], ev_k[2], ev_out[2];
-  for (int s = 0; s < 2; s++)
-  {
-    PCS_CUDA(cudaEventCreateWithFlags(&ev_in[s], cudaEventDisableTiming));
-    PCS_CUDA(cudaEventCreateWithFlags(&ev_k[s], cudaEventDisableTiming));
-    PCS_CUDA(cudaEventCreateWithFlags(&ev_out[s], cudaEventDisableTiming));
-  }
+  // events live in the context (created once): a per-call create/destroy would be most of a single frame's latency
+  cudaEvent_t* ev_in = ctx->pipe_event;
+  cudaEvent_t* ev_k = ctx->pipe_event + 2;
+  cudaEvent_t* ev_out = ctx->pipe_event + 4;
   int status = PCS_OK;
+  cudaError_t first_err = cudaSuccess;  // first failing runtime call of the pipeline (non-sticky errors included)
+  const char* first_what = "";
+#define PCS_PIPE(call)                                                                                                 \
+  do                                                                                                                   \
+  {                                                                                                                    \
+    cudaError_t e_ = (call);                                                                                           \
+    if (e_ != cudaSuccess && first_err == cudaSuccess)                                                                 \
+    {                                                                                                                  \
+      first_err = e_;                                                                                                  \
+      first_what = #call;                                                                                              \
+    }                                                                                                                  \
+  } while (0)
   cudaStream_t s_in = ctx->copy_stream[0], s_out = ctx->copy_stream[1];
-  for (size_t c = 0; c < n_chunks && status == PCS_OK; c++)
+  for (size_t c = 0; c < n_chunks && status == PCS_OK && first_err == cudaSuccess; c++)
   {
     const int s = (int)(c % (size_t)n_buf);
     const size_t f0 = c * chunk_frames;
     const size_t nf = (f0 + chunk_frames <= (size_t)n_frames) ? chunk_frames : (size_t)n_frames - f0;
     if (c >= (size_t)n_buf)
-      cudaStreamWaitEvent(s_in, ev_out[s], 0);  // buffer set free again
-    cudaMemcpyAsync(d_in[s], clouds + f0 * ppf, nf * frame_bytes, cudaMemcpyHostToDevice, s_in);
-    cudaEventRecord(ev_in[s], s_in);
-    cudaStreamWaitEvent(ctx->stream, ev_in[s], 0);
+      PCS_PIPE(cudaStreamWaitEvent(s_in, ev_out[s], 0));  // buffer set free again
+    PCS_PIPE(cudaMemcpyAsync(d_in[s], clouds + f0 * ppf, nf * frame_bytes, cudaMemcpyHostToDevice, s_in));
+    PCS_PIPE(cudaEventRecord(ev_in[s], s_in));
+    PCS_PIPE(cudaStreamWaitEvent(ctx->stream, ev_in[s], 0));
     status = annotate_dev(ctx, map, (const pcs_point_xyzrgb*)d_in[s], (int)nf, width, height,
                           d_pose ? (const float*)d_pose + f0 * 16 : nullptr, params,
                           annotated_out ? (pcs_point_xyzrgb*)d_ann[s] : nullptr, mask_out ? (uint8_t*)d_mask[s] : nullptr);
-    cudaEventRecord(ev_k[s], ctx->stream);
-    cudaStreamWaitEvent(s_out, ev_k[s], 0);
+    PCS_PIPE(cudaEventRecord(ev_k[s], ctx->stream));
+    PCS_PIPE(cudaStreamWaitEvent(s_out, ev_k[s], 0));
     if (annotated_out)
-      cudaMemcpyAsync(annotated_out + f0 * ppf, d_ann[s], nf * frame_bytes, cudaMemcpyDeviceToHost, s_out);
+      PCS_PIPE(cudaMemcpyAsync(annotated_out + f0 * ppf, d_ann[s], nf * frame_bytes, cudaMemcpyDeviceToHost, s_out));
     if (mask_out)
-      cudaMemcpyAsync(mask_out + f0 * ppf, d_mask[s], nf * ppf, cudaMemcpyDeviceToHost, s_out);
-    cudaEventRecord(ev_out[s], s_out);
+      PCS_PIPE(cudaMemcpyAsync(mask_out + f0 * ppf, d_mask[s], nf * ppf, cudaMemcpyDeviceToHost, s_out));
+    PCS_PIPE(cudaEventRecord(ev_out[s], s_out));
     ctx->stats.bytes_h2d += nf * frame_bytes;
     ctx->stats.bytes_d2h += (annotated_out ? nf * frame_bytes : 0) + (mask_out ? nf * ppf : 0);
   }
+#undef PCS_PIPE
   cudaError_t e1 = cudaStreamSynchronize(s_in), e2 = cudaStreamSynchronize(ctx->stream), e3 = cudaStreamSynchronize(s_out);
-  for (int s = 0; s < 2; s++)
-  {
-    cudaEventDestroy(ev_in[s]);
-    cudaEventDestroy(ev_k[s]);
-    cudaEventDestroy(ev_out[s]);
-  }
   if (status != PCS_OK)
     return status;
+  if (first_err != cudaSuccess)
+    return cuda_fail(first_err, first_what, __FILE__, __LINE__);
   PCS_CUDA(e1);
   PCS_CUDA(e2);
   PCS_CUDA(e3);

@@ -75,6 +75,7 @@ struct pcs_ctx
   cudaStream_t stream;
   bool owns_stream;
   cudaStream_t copy_stream[pcs::kCopyStreams];
+  cudaEvent_t pipe_event[6];  // H2D done / kernel done / D2H done per buffer set of the host-pointer pipelines
   // grow-only device scratch (block counts, flags, staging)
   void* scratch;
   size_t scratch_bytes;
@@ -213,6 +214,70 @@ __device__ __forceinline__ void map_add_warp(const MapView& m, bool valid, unsig
       map_add(m, key48, (unsigned long long)c0 | ((unsigned long long)c1 << 32));
     }
   }
+}
+
+// Split form of map_add_warp for kernels that hold several points per thread: _begin elects the leaders and issues the
+// load of each leader's home slot, _end completes the insert.  Calling _begin for all points before the first _end keeps
+// one table lookup (an L2 round trip) in flight per point instead of serialising them.
+struct MapProbe
+{
+  unsigned long long want, add, slot, k;
+  bool leader;
+};
+
+__device__ __forceinline__ MapProbe map_add_warp_begin(const MapView& m, bool valid, unsigned long long key48, bool cls1)
+{
+  MapProbe pr;
+  pr.leader = false;
+  pr.want = pr.add = pr.slot = pr.k = 0ull;
+  const unsigned active = __ballot_sync(0xffffffffu, valid);
+  const unsigned ones = __ballot_sync(0xffffffffu, valid && cls1);
+  if (valid)
+  {
+    const unsigned peers = __match_any_sync(active, key48);
+    const unsigned lane = threadIdx.x & 31u;
+    if ((unsigned)(__ffs(peers) - 1) == lane)
+    {
+      const unsigned c1 = __popc(peers & ones);
+      const unsigned c0 = __popc(peers) - c1;
+      pr.leader = true;
+      pr.add = (unsigned long long)c0 | ((unsigned long long)c1 << 32);
+      pr.want = key48 | kValidBit;
+      pr.slot = slot_hash(key48) & m.mask;
+      pr.k = ld_relaxed_u64(&m.slots[pr.slot].key);
+    }
+  }
+  return pr;
+}
+
+__device__ __forceinline__ void map_add_warp_end(const MapView& m, const MapProbe& pr)
+{
+  if (!pr.leader)
+    return;
+  unsigned long long slot = pr.slot, k = pr.k;
+#pragma unroll 1
+  for (unsigned int probe = 0; probe < 65536u; ++probe)
+  {
+    Slot* s = m.slots + slot;
+    if (probe)
+      k = ld_relaxed_u64(&s->key);
+    if (k == 0ull)
+    {
+      k = atomicCAS(&s->key, 0ull, pr.want);
+      if (k == 0ull)
+      {
+        atomicAdd(m.n_used, 1u);
+        k = pr.want;
+      }
+    }
+    if (k == pr.want)
+    {
+      atomicAdd(&s->counts, pr.add);
+      return;
+    }
+    slot = (slot + 1) & m.mask;
+  }
+  *m.overflow = 1u;
 }
 
 __device__ __forceinline__ bool color_pass(int r, int g, int b, int lower, int upper, int neg)

@@ -135,6 +135,8 @@ int pcs_ctx_create(int device, void* cuda_stream, pcs_ctx** out)
   }
   for (int i = 0; i < pcs::kCopyStreams; i++)
     PCS_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream[i], cudaStreamNonBlocking));
+  for (int i = 0; i < 6; i++)
+    PCS_CUDA(cudaEventCreateWithFlags(&ctx->pipe_event[i], cudaEventDisableTiming));
   PCS_CUDA(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
   *out = ctx;
   return PCS_OK;
@@ -155,6 +157,9 @@ int pcs_ctx_destroy(pcs_ctx* ctx)
     cudaFreeHost(ctx->pinned);
   if (ctx->hsv_tables_dev)
     cudaFree(ctx->hsv_tables_dev);
+  for (int i = 0; i < 6; i++)
+    if (ctx->pipe_event[i])
+      cudaEventDestroy(ctx->pipe_event[i]);
   for (int i = 0; i < pcs::kCopyStreams; i++)
     cudaStreamDestroy(ctx->copy_stream[i]);
   if (ctx->owns_stream)

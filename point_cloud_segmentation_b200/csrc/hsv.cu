@@ -2,10 +2,10 @@
 //
 // Replaces hsvThresholdingDetector (pcs_detection/include/pcs_detection/hsv_thresholding.h:45-70) and the detector
 // service body (pcs_ros/src/hsv_thresholding_node.cpp:8-28).  The HSV image the reference materialises never
-// exists: each block stages a tile of BGR rows in shared memory with 128-bit loads, thresholds it there, optionally
-// erodes/dilates it there, and writes the mask with 128-bit stores.
+// exists: the threshold runs on BGR rows staged with 128-bit loads (dense images: hsv_mask_flat_kernel), the optional
+// opening runs on bit-packed masks in shared memory (hsv_open_kernel), and the mask is written with wide stores.
 //
-// HBM-bound: 3 B read + 1 B written per pixel (4 B/px algorithmic; +9 % halo re-reads when the opening is on).
+// HBM-bound: 3 B read + 1 B written per pixel (4 B/px algorithmic; the opening re-reads a 4-pixel halo through L1/L2).
 #include "common.cuh"
 #include "hsv.cuh"
 
@@ -15,30 +15,28 @@ constexpr int kTileW = 128;
 constexpr int kTileH = 8;
 constexpr int kHsvThreads = 256;
 
-template <int HALO>
 struct TileGeom
 {
-  static constexpr int RW = kTileW + 2 * HALO;  // region width in pixels
-  static constexpr int RH = kTileH + 2 * HALO;
+  static constexpr int RW = kTileW;
+  static constexpr int RH = kTileH;
   static constexpr int ROW_BYTES = ((RW * 3 + 15) / 16) * 16 + 32;  // room for the 16-byte phase of the source
 };
 
-template <bool MORPH, int OUT_CH>
+// generic (pitched / unaligned / 3-channel output) threshold kernel, no opening
+template <int OUT_CH>
 __global__ void __launch_bounds__(kHsvThreads) hsv_mask_kernel(const uint8_t* __restrict__ bgr, int width, int height,
                                                               size_t stride, HsvBounds bounds, int inverted,
                                                               uint8_t* __restrict__ mask, size_t mask_stride)
 {
-  constexpr int HALO = MORPH ? 4 : 0;
-  using G = TileGeom<HALO>;
+  using G = TileGeom;
   __shared__ int s_lut[512];
   __shared__ __align__(16) uint8_t s_bgr[G::RH][G::ROW_BYTES];
   __shared__ uint8_t s_m[G::RH][G::RW + 4];
-  __shared__ uint8_t s_e[MORPH ? (kTileH + 4) : 1][MORPH ? (kTileW + 8) : 4];
 
   load_hsv_lut(s_lut);
 
-  const int x0 = blockIdx.x * kTileW - HALO;  // region origin (may be negative)
-  const int y0 = blockIdx.y * kTileH - HALO;
+  const int x0 = blockIdx.x * kTileW;
+  const int y0 = blockIdx.y * kTileH;
   const int xs = max(x0, 0), xe = min(x0 + G::RW, width);  // valid pixel columns [xs, xe)
 
   // ---- stage BGR rows: 16-byte chunks where the global address allows, bytes at the ragged ends ----------------
@@ -68,13 +66,13 @@ __global__ void __launch_bounds__(kHsvThreads) hsv_mask_kernel(const uint8_t* __
   }
   __syncthreads();
 
-  // ---- threshold the region -------------------------------------------------------------------------------------
+  // ---- threshold the tile -----------------------------------------------------------------------------------------
   for (int i = threadIdx.x; i < G::RH * G::RW; i += kHsvThreads)
   {
     const int r = i / G::RW, c = i - r * G::RW;
     const int x = x0 + c, y = y0 + r;
-    uint8_t m = 255;  // outside the image: does not constrain the erosion
-    if (x >= 0 && x < width && y >= 0 && y < height)
+    uint8_t m = 0;
+    if (x < width && y < height)
     {
       const uint8_t* row = bgr + (size_t)y * stride;
       const int phase = (int)((uintptr_t)(row + 3 * (size_t)xs) & 15u);
@@ -84,40 +82,6 @@ __global__ void __launch_bounds__(kHsvThreads) hsv_mask_kernel(const uint8_t* __
     s_m[r][c] = m;
   }
   __syncthreads();
-
-  if (MORPH)
-  {
-    // erosion over the tile grown by 2; positions outside the image become 0 so the dilation ignores them
-    for (int i = threadIdx.x; i < (kTileH + 4) * (kTileW + 4); i += kHsvThreads)
-    {
-      const int r = i / (kTileW + 4), c = i - r * (kTileW + 4);
-      const int x = x0 + 2 + c, y = y0 + 2 + r;
-      uint8_t e = 0;
-      if (x >= 0 && x < width && y >= 0 && y < height)
-      {
-        e = 255;
-#pragma unroll
-        for (int dy = 0; dy < 5; dy++)
-#pragma unroll
-          for (int dx = 0; dx < 5; dx++)
-            e = min(e, s_m[r + dy][c + dx]);
-      }
-      s_e[r][c] = e;
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < kTileH * kTileW; i += kHsvThreads)
-    {
-      const int r = i / kTileW, c = i - r * kTileW;
-      uint8_t d = 0;
-#pragma unroll
-      for (int dy = 0; dy < 5; dy++)
-#pragma unroll
-        for (int dx = 0; dx < 5; dx++)
-          d = max(d, s_e[r + dy][c + dx]);
-      s_bgr[r][c] = d;  // reuse the BGR staging area as the output tile (row pitch ROW_BYTES >= kTileW)
-    }
-    __syncthreads();
-  }
 
   // ---- write the tile ---------------------------------------------------------------------------------------------
   const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
@@ -134,7 +98,7 @@ __global__ void __launch_bounds__(kHsvThreads) hsv_mask_kernel(const uint8_t* __
       uint8_t v[16];
 #pragma unroll
       for (int k = 0; k < 16; k++)
-        v[k] = (MORPH ? s_bgr[r][cg + k] : s_m[r][cg + k]) ^ inv;
+        v[k] = s_m[r][cg + k] ^ inv;
       uint8_t* out = mask + (size_t)y * mask_stride + x;
       if (x + 16 <= width && (((uintptr_t)out) & 15u) == 0)
       {
@@ -155,11 +119,153 @@ __global__ void __launch_bounds__(kHsvThreads) hsv_mask_kernel(const uint8_t* __
       const int y = ty0 + r, x = tx0 + c;
       if (y >= height || x >= width)
         continue;
-      const uint8_t v = (MORPH ? s_bgr[r][c] : s_m[r][c]) ^ inv;
+      const uint8_t v = s_m[r][c] ^ inv;
       uint8_t* out = mask + (size_t)y * mask_stride + 3 * (size_t)x;
       out[0] = v;
       out[1] = v;
       out[2] = v;
+    }
+  }
+}
+
+// ---- threshold + 5x5 opening on bit-packed masks ------------------------------------------------------------------------
+// A CTA takes a tile of 256 columns x tile_h (<= 64) rows.  Phase A thresholds the tile grown by 4 pixels on every side
+// (the opening's 9x9 dependency) and packs the result with warp ballots: 32 pixels per word, 10 words per row (word 0 /
+// word 9 carry the 4 halo columns).  Phase B opens the packed rows separably: a 5-wide min is 4 shifts + 4 ANDs of a
+// 64-bit window, a 5-tall min is 4 ANDs across lanes that each hold one row (shuffles); dilation likewise with ORs.  Each
+// warp owns 32 columns and produces 24 finished rows per step from 32 thresholded rows.  cv2's border rule: pixels
+// outside the image take no part = thresholded pixels outside count as 1 for the erosion, eroded pixels outside as 0.
+constexpr int kOpenImgTW = 256;
+constexpr int kOpenImgMaxTH = 64;
+constexpr int kOpenImgWords = kOpenImgTW / 32 + 2;
+
+template <int OUT_CH>
+__global__ void __launch_bounds__(kOpenImgTW) hsv_open_kernel(const uint8_t* __restrict__ bgr, int width, int height,
+                                                            size_t stride, HsvBounds bounds, int inverted,
+                                                            uint8_t* __restrict__ mask, size_t mask_stride, int tile_h)
+{
+  __shared__ int s_lut[512];
+  __shared__ unsigned int s_raw[kOpenImgMaxTH + 8][kOpenImgWords];
+  load_hsv_lut(s_lut);
+  const unsigned int tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const int x0 = blockIdx.x * kOpenImgTW, y0 = blockIdx.y * tile_h;
+  const int rows_out = min(tile_h, height - y0);
+  const int R = rows_out + 8;  // thresholded rows e = 0 .. R-1 <-> image rows y0 - 4 + e
+  __syncthreads();
+
+  // ---- A: threshold + pack ------------------------------------------------------------------------------------------------
+  {
+    const int col = x0 + (int)tid;
+    const bool col_ok = col < width;
+    const uint8_t* px0 = bgr + 3 * (size_t)(col_ok ? col : 0);
+#pragma unroll 4
+    for (int e = 0; e < R; e++)
+    {
+      const int y = y0 - 4 + e;
+      bool bit = true;
+      if (col_ok && y >= 0 && y < height)
+      {
+        const uint8_t* px = px0 + (size_t)y * stride;
+        bit = hsv_in_range(s_lut, __ldg(px), __ldg(px + 1), __ldg(px + 2), bounds);
+      }
+      const unsigned int word = __ballot_sync(0xffffffffu, bit);
+      if (lane == 0)
+        s_raw[e][1 + warp] = word;
+    }
+    // halo columns: pair p = 8 * row + halo column, 32 pairs (4 rows) per warp pass
+    for (int p = (int)tid; p < ((R * 8 + 31) & ~31); p += kOpenImgTW)
+    {
+      const int e = p >> 3, hc = p & 7;
+      const int y = y0 - 4 + e;
+      const int hcol = hc < 4 ? x0 - 4 + hc : x0 + kOpenImgTW + (hc - 4);
+      bool bit = true;
+      if (e < R && y >= 0 && y < height && hcol >= 0 && hcol < width)
+      {
+        const uint8_t* px = bgr + (size_t)y * stride + 3 * (size_t)hcol;
+        bit = hsv_in_range(s_lut, __ldg(px), __ldg(px + 1), __ldg(px + 2), bounds);
+      }
+      const unsigned int hb = __ballot_sync(0xffffffffu, bit);
+      const int er = ((p & ~31) >> 3) + (int)lane;  // lanes 0..3 store the 4 rows of this pass
+      if (lane < 4u && er < R)
+      {
+        const unsigned int byte = (hb >> (8u * lane)) & 0xffu;
+        s_raw[er][0] = (byte & 0xfu) << 28;
+        s_raw[er][kOpenImgWords - 1] = byte >> 4;
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- B + C: open 32 columns x 24 rows per step, write them ------------------------------------------------------------------
+  unsigned long long col_valid = ~0ull;  // columns [x0 + 32 warp - 16, +64) inside the image
+  {
+    const int lo = x0 + 32 * (int)warp - 16;
+    if (lo < 0)
+      col_valid &= ~0ull << (-lo);
+    const int n = width - lo;
+    if (n < 64)
+      col_valid &= (n <= 0) ? 0ull : ((1ull << n) - 1ull);
+  }
+  const unsigned int inv4 = inverted ? 0xffffffffu : 0u;
+  for (int eb = 0; eb < rows_out; eb += 24)
+  {
+    const unsigned int* rr = s_raw[min(eb + (int)lane, R - 1)];
+    const unsigned long long win =
+        ((unsigned long long)rr[warp] >> 16) | ((unsigned long long)rr[warp + 1] << 16) | ((unsigned long long)rr[warp + 2] << 48);
+    // 5-wide min in three shift/AND steps: pairs, triples (bits i .. i+2), then the triples at i-2 and at i
+    const unsigned long long w2 = win & (win >> 1), w3 = w2 & (win >> 2);
+    const unsigned long long he = w3 & (w3 << 2);
+    unsigned long long er5 = he;  // lane l <= 27: eroded row e = eb + 2 + l
+#pragma unroll
+    for (int d = 1; d <= 4; d++)
+      er5 &= __shfl_down_sync(0xffffffffu, he, d);
+    const int y_e = y0 - 4 + eb + 2 + (int)lane;
+    er5 = (y_e >= 0 && y_e < height) ? (er5 & col_valid) : 0ull;
+    const unsigned long long d2 = er5 | (er5 >> 1), d3 = d2 | (er5 >> 2);
+    const unsigned long long hd = d3 | (d3 << 2);
+    unsigned long long op = hd;  // lane l <= 23: opened row e = eb + 4 + l <-> image row y0 + eb + l
+#pragma unroll
+    for (int d = 1; d <= 4; d++)
+      op |= __shfl_down_sync(0xffffffffu, hd, d);
+    const unsigned int fin = (unsigned int)(op >> 16);
+
+    if (OUT_CH == 1)
+    {
+      // 4 rows per pass: lane = 8 * row + group of 4 pixels -> one 32-bit store (bytes when the address is not aligned)
+      const int i = (int)(lane >> 3), g4 = (int)(lane & 7u) * 4;
+#pragma unroll
+      for (int q = 0; q < 6; q++)
+      {
+        const int ri = 4 * q + i;
+        const unsigned int word = __shfl_sync(0xffffffffu, fin, ri);
+        const int y = y0 + eb + ri, x = x0 + 32 * (int)warp + g4;
+        if (eb + ri >= rows_out || x >= width)
+          continue;
+        const unsigned int nib = (word >> g4) & 0xfu;
+        const unsigned int bytes = (((nib * 0x00204081u) & 0x01010101u) * 0xffu) ^ inv4;
+        uint8_t* out = mask + (size_t)y * mask_stride + x;
+        if (x + 4 <= width && (((uintptr_t)out) & 3u) == 0)
+          *reinterpret_cast<unsigned int*>(out) = bytes;
+        else
+          for (int k = 0; k < 4 && x + k < width; k++)
+            out[k] = (uint8_t)(bytes >> (8 * k));
+      }
+    }
+    else
+    {
+#pragma unroll 4
+      for (int ri = 0; ri < 24; ri++)
+      {
+        const unsigned int word = __shfl_sync(0xffffffffu, fin, ri);
+        const int y = y0 + eb + ri, x = x0 + (int)tid;
+        if (eb + ri >= rows_out || x >= width)
+          continue;
+        const uint8_t v = (uint8_t)((((word >> lane) & 1u) ? 255u : 0u) ^ (inv4 & 0xffu));
+        uint8_t* out = mask + (size_t)y * mask_stride + 3 * (size_t)x;
+        out[0] = v;
+        out[1] = v;
+        out[2] = v;
+      }
     }
   }
 }
@@ -184,12 +290,6 @@ __global__ void __launch_bounds__(kHsvThreads) hsv_mask_kernel(const uint8_t* __
 constexpr int kFastThreads = 256;
 constexpr int kFastPxPerThread = 16;
 constexpr int kFastPxPerCta = kFastThreads * kFastPxPerThread;  // 4096
-
-struct HsvDecisionTables
-{
-  uint32_t vs[256];  // first diff | count << 16
-  int2 hx[256];      // each component: (uint16) first X (two's complement) | count << 16
-};
 
 // false if the thresholds cannot be expressed (never the case for an interval of hues; kept as a guard)
 static bool build_decision_tables(const pcs_hsv_params& p, HsvDecisionTables& t)
@@ -239,20 +339,6 @@ static bool build_decision_tables(const pcs_hsv_params& p, HsvDecisionTables& t)
     t.hx[diff].y = (int)(((uint32_t)start[1] & 0xffffu) | ((uint32_t)count[1] << 16));
   }
   return true;
-}
-
-__device__ __forceinline__ uint32_t decide(const uint32_t* __restrict__ s_vs, const int2* __restrict__ s_hx, int b, int g,
-                                           int r)
-{
-  const int v = max(max(b, g), r);
-  const int diff = v - min(min(b, g), r);
-  const int X = (v == r) ? (g - b) : ((v == g) ? (b - r + 2 * diff) : (r - g + 4 * diff));
-  const uint32_t e = s_vs[v];
-  const int2 hh = s_hx[diff];
-  const bool ok_vs = (uint32_t)(diff - (int)(e & 0xffffu)) < (e >> 16);
-  const bool ok_h = ((uint32_t)(X - (int)(short)(hh.x & 0xffff)) < ((uint32_t)hh.x >> 16)) |
-                    ((uint32_t)(X - (int)(short)(hh.y & 0xffff)) < ((uint32_t)hh.y >> 16));
-  return (ok_vs & ok_h) ? 0xffu : 0u;
 }
 
 __global__ void __launch_bounds__(kFastThreads) hsv_mask_flat_kernel(const uint8_t* __restrict__ bgr, unsigned long long n_px,
@@ -321,7 +407,7 @@ __global__ void __launch_bounds__(kFastThreads) hsv_mask_flat_kernel(const uint8
 }
 
 // device copy of the decision tables for `p`, cached in the context; *out = NULL if `p` cannot be tabulated
-static int flat_tables(pcs_ctx* ctx, const pcs_hsv_params& p, const HsvDecisionTables** out)
+int hsv_decision_tables(pcs_ctx* ctx, const pcs_hsv_params& p, const HsvDecisionTables** out)
 {
   *out = nullptr;
   const bool same = ctx->hsv_tables_valid && ctx->hsv_tables_params.h_lo == p.h_lo && ctx->hsv_tables_params.h_hi == p.h_hi &&
@@ -357,7 +443,7 @@ int launch_hsv_mask(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, int height,
   if (flat)
   {
     const HsvDecisionTables* tables = nullptr;
-    PCS_TRY(flat_tables(ctx, *p, &tables));
+    PCS_TRY(hsv_decision_tables(ctx, *p, &tables));
     if (tables)
     {
       const unsigned long long n_px = (unsigned long long)width * height;
@@ -369,18 +455,23 @@ int launch_hsv_mask(pcs_ctx* ctx, const uint8_t* bgr_dev, int width, int height,
   }
   if (p->morph_open)
   {
+    // tile height: 64 rows keep the halo at 8 / 64; small images get shorter tiles so that the grid covers the SMs
+    const unsigned int bands = (unsigned)((width + kOpenImgTW - 1) / kOpenImgTW);
+    int tile_h = kOpenImgMaxTH;
+    while (tile_h > 8 && (unsigned long long)bands * ((height + tile_h - 1) / tile_h) < 2ull * (unsigned long long)ctx->sm_count)
+      tile_h >>= 1;
+    dim3 ogrid(bands, (unsigned)((height + tile_h - 1) / tile_h));
     if (out_channels == 1)
-      hsv_mask_kernel<true, 1><<<grid, block, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride);
+      hsv_open_kernel<1><<<ogrid, kOpenImgTW, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride, tile_h);
     else
-      hsv_mask_kernel<true, 3><<<grid, block, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride);
+      hsv_open_kernel<3><<<ogrid, kOpenImgTW, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride, tile_h);
+    count_launch(ctx);
+    return check_launch("hsv_open_kernel");
   }
+  if (out_channels == 1)
+    hsv_mask_kernel<1><<<grid, block, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride);
   else
-  {
-    if (out_channels == 1)
-      hsv_mask_kernel<false, 1><<<grid, block, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride);
-    else
-      hsv_mask_kernel<false, 3><<<grid, block, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride);
-  }
+    hsv_mask_kernel<3><<<grid, block, 0, ctx->stream>>>(bgr_dev, width, height, stride, b, inv, mask_dev, mask_stride);
   count_launch(ctx);
   return check_launch("hsv_mask_kernel");
 }

@@ -81,4 +81,31 @@ __device__ __forceinline__ bool hsv_in_range(const int* __restrict__ s_lut, int 
   h += (h < 0) ? 180 : 0;
   return (h >= p.h_lo) & (h <= p.h_hi) & (s >= p.s_lo) & (s <= p.s_hi) & (v >= p.v_lo) & (v <= p.v_hi);
 }
+
+// Decision tables of the threshold for one set of bounds, built on the host by exact enumeration (hsv.cu,
+// build_decision_tables): a pixel then costs max3 / min3, the hue numerator, two table reads and four compares.
+struct HsvDecisionTables
+{
+  uint32_t vs[256];  // first diff | count << 16
+  int2 hx[256];      // each component: (uint16) first X (two's complement) | count << 16
+};
+
+
+__device__ __forceinline__ uint32_t decide(const uint32_t* __restrict__ s_vs, const int2* __restrict__ s_hx, int b, int g,
+                                           int r)
+{
+  const int v = max(max(b, g), r);
+  const int diff = v - min(min(b, g), r);
+  const int X = (v == r) ? (g - b) : ((v == g) ? (b - r + 2 * diff) : (r - g + 4 * diff));
+  const uint32_t e = s_vs[v];
+  const int2 hh = s_hx[diff];
+  const bool ok_vs = (uint32_t)(diff - (int)(e & 0xffffu)) < (e >> 16);
+  const bool ok_h = ((uint32_t)(X - (int)(short)(hh.x & 0xffff)) < ((uint32_t)hh.x >> 16)) |
+                    ((uint32_t)(X - (int)(short)(hh.y & 0xffff)) < ((uint32_t)hh.y >> 16));
+  return (ok_vs & ok_h) ? 0xffu : 0u;
+}
+
+
+// device copy of the decision tables for `p`, cached in the context; *out = NULL if `p` cannot be tabulated
+int hsv_decision_tables(pcs_ctx* ctx, const pcs_hsv_params& p, const HsvDecisionTables** out);
 }  // namespace pcs

@@ -99,11 +99,18 @@ __device__ bool tri_box_overlap(const double* lo, const double* hi, const double
 __device__ __forceinline__ double vox_lo(int k, double res) { return (double)(k - 32768) * res; }
 __device__ __forceinline__ double vox_hi(int k, double res) { return (double)(k - 32767) * res; }
 
-// exact interval of keys whose closed extent meets [tmin, tmax]; false if empty / non-finite
+// exact interval of keys whose closed extent meets [tmin, tmax]; false if empty / non-finite.
+// The interval is clamped to the key range first, so the floor estimate is at most one or two voxels off and the
+// correction loops below run a bounded number of steps however far away a (finite) vertex lies.
 __device__ bool key_range(double tmin, double tmax, double res, double inv, int& klo, int& khi)
 {
   if (!isfinite(tmin) || !isfinite(tmax))
     return false;
+  const double range_lo = vox_lo(0, res), range_hi = vox_hi(65535, res);
+  if (tmin > range_hi || tmax < range_lo)
+    return false;  // entirely outside the map's key range: no voxel can touch it
+  tmin = fmax(tmin, range_lo);
+  tmax = fmin(tmax, range_hi);
   double e = floor(tmin * inv);
   e = fmin(fmax(e, -40000.0), 40000.0);
   int k = (int)e + 32768;

@@ -18,8 +18,11 @@
 //     next call starts.  Nothing in it has to start at zero -- every word a call reads was written earlier in that
 //     same call -- so there is nothing to clear, but two calls whose kernels overlap on the GPU (different streams or
 //     different contexts on one device) overwrite each other's counts: keep such calls ordered;
+//   * the input and output point ranges must not overlap (no in-place filtering): the call refuses them;
 //   * the first call on a device looks up the array's device address (cudaGetSymbolAddress, once per device, with that
-//     device current).  Make that first call before starting any stream capture.
+//     device current).  Under CUDA's lazy module loading that first call is also where the driver loads this library's
+//     device code onto the GPU, which is the one moment the driver itself may reserve memory on the call's behalf.
+//     Make that first call early, before the latency-critical phase and before starting any stream capture.
 // Host code must never hand the array's name to a kernel: on the host the name is only a handle for the runtime, not
 // a device address.  Everything below goes through the looked-up pointer.
 #include <mutex>
@@ -111,6 +114,14 @@ extern "C" int pcs_color_passthrough_noalloc_dev(pcs_ctx* ctx, const pcs_point_x
   }
   PCS_CHECK_ARG(in_dev && out_dev, "NULL point buffer");
   PCS_CHECK_ARG(((uintptr_t)in_dev & 15u) == 0 && ((uintptr_t)out_dev & 15u) == 0, "point buffers must be 16-byte aligned");
+  PCS_CHECK_ARG(((uintptr_t)n_out_dev & 7u) == 0, "n_out_dev must be 8-byte aligned");
+  {
+    // The scatter pass writes out[dst <= i] while other blocks still read `in` and re-evaluates the filter on it, so an
+    // in-place call would corrupt the result silently: refuse any overlap of the two point ranges.
+    const uintptr_t a0 = (uintptr_t)in_dev, a1 = a0 + (uintptr_t)n * sizeof(pcs_point_xyzrgb);
+    const uintptr_t b0 = (uintptr_t)out_dev, b1 = b0 + (uintptr_t)n * sizeof(pcs_point_xyzrgb);
+    PCS_CHECK_ARG(a1 <= b0 || b1 <= a0, "in_dev and out_dev overlap: the filter cannot run in place");
+  }
   if (compact_scratch_bytes(n) > kScratchBytes)  // cannot happen for n <= kMaxPoints; guards a future layout change
   {
     set_error("internal: fixed scratch array too small for %llu points", (unsigned long long)n);

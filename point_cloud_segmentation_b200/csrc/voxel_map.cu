@@ -228,9 +228,9 @@ static int read_counters(pcs_ctx* ctx, pcs_map* map, unsigned int out[2])
   PCS_CUDA(cudaStreamSynchronize(ctx->stream));
   out[0] = ((unsigned int*)h)[0];
   out[1] = ((unsigned int*)h)[1];
-  if (out[1])
+  if (out[1] || out[0] > map->capacity_voxels)
   {
-    set_error("voxel map overflow: more than %llu distinct voxels", (unsigned long long)map->capacity_voxels);
+    set_error("voxel map overflow: %u distinct voxels, capacity %llu", out[0], (unsigned long long)map->capacity_voxels);
     return PCS_ERR_CAPACITY;
   }
   return PCS_OK;

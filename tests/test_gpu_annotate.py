@@ -122,6 +122,40 @@ def test_detector_options_inverted_and_opening(ctx, pcs, O):
         vmap.destroy()
 
 
+@pytest.mark.parametrize("w,h,n_frames,section_rows", [(700, 420, 2, 0), (300, 200, 3, 180), (513, 97, 1, 0), (256, 33, 2, 12),
+                                                        (260, 64, 1, 64), (1283, 50, 1, 0)])
+def test_fused_opening_bands_and_sections(ctx, pcs, O, monkeypatch, w, h, n_frames, section_rows):
+    """The opening needs a 9x9 neighbourhood: bands of 256 columns and row sections must stitch without seams, at frame
+    borders and at every band / section boundary, with all outputs (mask, annotated cloud, voxel counts)."""
+    if section_rows:
+        monkeypatch.setenv("PCS_OPEN_SECTION_ROWS", str(section_rows))
+    res = 0.01
+    frames, poses = make_scan(O, n_frames, w, h)
+    rng = np.random.default_rng(w * h)
+    # blobs and speckles around the threshold colour so that the opening removes and keeps things everywhere
+    hit = rng.random(frames.size) < 0.55
+    frames["b"][hit], frames["g"][hit], frames["r"][hit] = 140, 90, 50
+    for inverted in (0, 1):
+        vmap = ctx.create_map(res, 1 << 17)
+        p = pcs.annotate_params(pcs.hsv_params(inverted=inverted, morph_open=1), lower=255, upper=255)
+        ann, mask = ctx.annotate_frames(frames, n_frames, w, h, poses, p, vmap)
+        op = O.default_params(inverted=inverted, morph_open=1)
+        o_ann, o_mask, o_keys, o_c0, o_c1 = oracle_scan(O, frames, poses, n_frames, w, h, res, 255, 255, False, op)
+        assert np.array_equal(mask, o_mask)
+        assert 0.02 < (o_mask == 255).mean() < 0.98
+        assert same_bytes(ann, o_ann)
+        keys, c0, c1, _ = vmap.export()
+        assert np.array_equal(keys, o_keys) and np.array_equal(c1, o_c1) and np.array_equal(c0, o_c0)
+        # mask-only and map-only variants of the kernel give the same answers
+        _, mask2 = ctx.annotate_frames(frames, n_frames, w, h, poses, p, None, want_annotated=False)
+        assert np.array_equal(mask2, o_mask)
+        vmap.clear()
+        ctx.annotate_frames(frames, n_frames, w, h, poses, p, vmap, want_annotated=False, want_mask=False)
+        k2, a0, a1, _ = vmap.export()
+        assert np.array_equal(k2, o_keys) and np.array_equal(a1, o_c1) and np.array_equal(a0, o_c0)
+        vmap.destroy()
+
+
 def test_nan_inf_and_out_of_range_points_are_culled(ctx, pcs, O):
     rng = np.random.default_rng(11)
     w, h = 200, 50

@@ -122,6 +122,35 @@ def test_vertices_on_voxel_faces_and_degenerate_triangles(ctx, pcs, O):
     vmap.destroy()
 
 
+def far_vertex_case():
+    """Finite vertices far outside the key range: 1e6 m, 1e30 m, DBL_MAX; some triangles reach back in."""
+    res = 0.005
+    kk = np.array([[32768 + i, 32768, 32768] for i in range(-3, 4)] + [[65535, 32768, 32768], [0, 32768, 32768]])
+    keys = (kk[:, 2].astype(np.uint64) << np.uint64(32)) | (kk[:, 1].astype(np.uint64) << np.uint64(16)) | kk[:, 0].astype(np.uint64)
+    big = np.finfo(np.float64).max
+    verts = np.array([
+        [1e6, 1e6, 1e6], [1e6 + 1, 1e6, 1e6], [1e6, 1e6 + 1, 1e6],            # 0-2   far, all axes
+        [1e30, 1e30, 1e30], [-1e30, 2e30, 1e30], [1e30, -1e30, 3e30],        # 3-5   very far, mixed signs
+        [big, big, big], [-big, -big, big], [big, -big, big],                # 6-8   DBL_MAX (z stays outside the key range)
+        [0.001, 0.001, 0.001], [1e30, 0.002, 0.002], [-1e30, 0.003, 0.001],  # 9-11  thin sliver along x through the map
+        [0.001, 1e6, 0.001], [0.002, 2e6, 0.001], [0.001, 1.5e6, 0.002],     # 12-14 far on y only
+        [0.0, 0.0, 0.0], [0.004, 0.0, 0.0], [0.0, 0.004, 0.004],             # 15-17 an ordinary hit
+    ])
+    tris = np.array([[0, 1, 2], [3, 4, 5], [6, 7, 8], [9, 10, 11], [12, 13, 14], [15, 16, 17], [9, 10, 10], [3, 3, 3]])
+    return res, keys, verts, faces4_of(tris)
+
+
+def test_far_vertices_terminate_and_match_the_oracle(ctx, pcs, O):
+    res, keys, verts, faces = far_vertex_case()
+    vmap = ctx.create_map(res, 1024)
+    vmap.merge(keys, None, np.ones(keys.size, np.uint32))
+    o_flags = O.mesh_contacts_keys(keys, res, verts, faces)
+    _, _, _, flags = ctx.mesh_mask(vmap, verts, faces, pcs.RETURN_COLORIZED)
+    assert np.array_equal(flags, o_flags)
+    assert flags.tolist() == [0, 0, 0, 1, 0, 1, 1, 0]
+    vmap.destroy()
+
+
 def test_empty_mesh_and_bad_mask_type(ctx, pcs):
     vmap = ctx.create_map(0.1, 64)
     ov, of, rgb, flags = ctx.mesh_mask(vmap, np.zeros((0, 3)), np.zeros((0, 4), np.int32), pcs.RETURN_OUTSIDE)

@@ -122,3 +122,12 @@ def test_loaders_on_reference_files(O):
     assert v.shape[0] == 6273 and f.size == 12288 * 4  # octomap_mesh_masking_unit.cpp:76-77
     v, f = O.load_ply_ascii(open(os.path.join(REF, "box_2m.ply"), "rb").read())
     assert v.shape[0] == 8 and f.size == 12 * 4  # :85-86
+
+
+def test_far_vertices_terminate(O):
+    """Vertices at 1e6 .. DBL_MAX metres must not spin the key-range walk (bounded by clamping to the key range)."""
+    from test_gpu_mesh import far_vertex_case
+
+    res, keys, verts, faces = far_vertex_case()
+    flags = O.mesh_contacts_keys(keys, res, verts, faces)
+    assert flags.tolist() == [0, 0, 0, 1, 0, 1, 1, 0]

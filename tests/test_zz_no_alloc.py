@@ -8,7 +8,7 @@ Collected last (file name) so that a -x run has already executed every other tes
 import numpy as np
 import pytest
 
-from util import random_cloud
+from util import random_cloud, same_bytes
 
 pytestmark = pytest.mark.gpu
 
@@ -26,7 +26,7 @@ def run_noalloc(ctx, pcs, cloud, lower, upper, neg, bufs):
     return out
 
 
-def test_two_calls_in_a_row_match_the_allocating_entry_point(ctx, pcs):
+def test_two_calls_in_a_row_match_the_allocating_entry_point(ctx, pcs, O):
     rng = np.random.default_rng(2023)
     n1, n2 = 300007, 4099  # big first, small second: stale counts of call 1 sit beyond call 2's blocks
     a = random_cloud(pcs.POINT_DTYPE, n1, rng)
@@ -43,6 +43,9 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point(ctx, pcs):
     assert 0 < want_a.size < n1 and 0 < want_b.size < n2
     assert got_a.tobytes() == want_a.tobytes()
     assert got_b.tobytes() == want_b.tobytes()
+    # and against the CPU oracle directly, so the chain does not rest on the sibling entry point alone
+    assert same_bytes(got_a, O.color_passthrough(a, 30, 200, False))
+    assert same_bytes(got_b, O.color_passthrough(b, 90, 160, True))
     # empty input: the count is cleared, nothing else is touched
     ctx.color_passthrough_noalloc_dev(bufs[0], 0, 0, 255, False, bufs[1], bufs[2])
     cnt = np.ones(1, np.uint64)
@@ -60,5 +63,8 @@ def test_sizes_beyond_the_fixed_array_are_refused(ctx, pcs):
     with pytest.raises(pcs.PcsError) as e:
         ctx.color_passthrough_noalloc_dev(bufs[0], 2, 9, 3, False, bufs[1], bufs[2])
     assert e.value.status == pcs.capi.PCS_ERR_BAD_ARG
+    with pytest.raises(pcs.PcsError) as e:  # in-place filtering would corrupt the output silently: refused
+        ctx.color_passthrough_noalloc_dev(bufs[0], 2, 0, 255, False, bufs[0] + 32, bufs[2])
+    assert e.value.status == pcs.capi.PCS_ERR_BAD_ARG and "overlap" in str(e.value)
     for p in bufs:
         ctx.dev_free(p)
