@@ -287,7 +287,17 @@ PCS_API int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* co
 PCS_API int pcs_mesh_mask(pcs_ctx* ctx, pcs_map* map, const double* verts, uint64_t nv, const int32_t* faces4,
                           uint64_t nt, int mask_type, uint64_t out_cap_tris, double* out_verts, int32_t* out_faces4,
                           uint8_t* out_rgb, uint8_t* tri_flags, uint64_t* n_out_verts, uint64_t* n_out_tris);
-/* Device-resident form used by the benchmark: flags only (1 byte per triangle) + number of contacted triangles. */
+/* Device-resident forms (mesh and outputs stay in HBM, work is enqueued on the context's stream).
+ * pcs_mesh_mask_dev: the whole of maskMesh -- contact flags, then the order-preserving compaction that emits the kept
+ *   triangles (INSIDE / OUTSIDE: 3 un-welded vertices, one face [3, 3i, 3i+1, 3i+2] and 9 colour bytes per kept triangle,
+ *   up to out_cap_tris of them; the kept count, which may exceed out_cap_tris, lands in *n_out_tris_dev) or the per-vertex
+ *   colours (COLORIZED: out_rgb_dev holds nv * 3 bytes, vertices / faces are the input's and are not copied).  The output
+ *   pointers may be NULL to count only.  tri_flags_dev (nt bytes) is required.
+ * pcs_mesh_contacts_dev: the contact flags only (1 byte per triangle). */
+PCS_API int pcs_mesh_mask_dev(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev,
+                              uint64_t nt, int mask_type, uint64_t out_cap_tris, double* out_verts_dev,
+                              int32_t* out_faces4_dev, uint8_t* out_rgb_dev, uint8_t* tri_flags_dev,
+                              uint64_t* n_out_tris_dev);
 PCS_API int pcs_mesh_contacts_dev(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv,
                                   const int32_t* faces4_dev, uint64_t nt, uint8_t* tri_flags_dev);
 

@@ -99,6 +99,7 @@ SIGNATURES = {
     "pcs_map_ipc_open": (_i, [_vp, _vp, _dbl, _u64, _pp]),
     "pcs_map_push_to_owners_dev": (_i, [_vp, _vp, _pp, _i]),
     "pcs_mesh_mask": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _i, _u64, _vp, _vp, _vp, _vp, _pu64, _pu64]),
+    "pcs_mesh_mask_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _i, _u64, _vp, _vp, _vp, _vp, _vp]),
     "pcs_mesh_contacts_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _vp]),
     "pcs_synth_frames_dev": (_i, [_vp, _u64, _i, _i, _i, _i, _vp, _vp]),
 }
@@ -486,6 +487,14 @@ class Context:
         _check(self.lib.pcs_mesh_mask(self.h, vmap.h, _p(verts), nv, _p(faces4), nt, int(mask_type), max(n_t, 1), _p(ov),
                                       _p(of), _p(rgb), _p(flags), C.byref(nov), C.byref(nom)))
         return ov[:n_v], of[:n_t], rgb[:n_v], flags
+
+    def mesh_mask_dev(self, vmap: VoxelMap, verts_dev: int, nv: int, faces4_dev: int, nt: int, mask_type: int, cap_tris: int,
+                      out_verts_dev: int | None, out_faces4_dev: int | None, out_rgb_dev: int | None, flags_dev: int,
+                      n_out_dev: int | None):
+        """Device-resident maskMesh: flags + compacted output (or colours), asynchronous on the context's stream."""
+        _check(self.lib.pcs_mesh_mask_dev(self.h, vmap.h, _p(verts_dev), int(nv), _p(faces4_dev), int(nt), int(mask_type),
+                                          int(cap_tris), _p(out_verts_dev), _p(out_faces4_dev), _p(out_rgb_dev), _p(flags_dev),
+                                          _p(n_out_dev)))
 
     def mesh_contacts_dev(self, vmap: VoxelMap, verts_dev: int, nv: int, faces4_dev: int, nt: int, flags_dev: int):
         _check(self.lib.pcs_mesh_contacts_dev(self.h, vmap.h, _p(verts_dev), int(nv), _p(faces4_dev), int(nt),

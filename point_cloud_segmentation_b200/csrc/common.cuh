@@ -90,6 +90,7 @@ struct pcs_ctx
   void* hsv_tables_dev;
   pcs_hsv_params hsv_tables_params;
   bool hsv_tables_valid;
+  void* mesh_counters;  // [0] big-triangle count, [1] finished CTAs of mesh_contacts_big_kernel; zero between calls
 };
 
 namespace pcs

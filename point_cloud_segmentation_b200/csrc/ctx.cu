@@ -157,6 +157,8 @@ int pcs_ctx_destroy(pcs_ctx* ctx)
     cudaFreeHost(ctx->pinned);
   if (ctx->hsv_tables_dev)
     cudaFree(ctx->hsv_tables_dev);
+  if (ctx->mesh_counters)
+    cudaFree(ctx->mesh_counters);
   for (int i = 0; i < 6; i++)
     if (ctx->pipe_event[i])
       cudaEventDestroy(ctx->pipe_event[i]);

@@ -49,7 +49,7 @@ __device__ __forceinline__ bool point_in_box(const double* lo, const double* hi,
 }
 
 // closed triangle / axis-aligned box overlap; same operation order as orc_tri_box_overlap
-__device__ bool tri_box_overlap(const double* lo, const double* hi, const double* v0, const double* v1, const double* v2)
+__device__ __noinline__ bool tri_box_overlap(const double* lo, const double* hi, const double* v0, const double* v1, const double* v2)
 {
 #pragma unroll
   for (int a = 0; a < 3; a++)
@@ -177,96 +177,349 @@ __device__ __forceinline__ void load_tri(const double* __restrict__ verts, unsig
     d.ok = key_range(dmin3(d.v0[a], d.v1[a], d.v2[a]), dmax3(d.v0[a], d.v1[a], d.v2[a]), res, inv, d.lo[a], d.hi[a]) && d.ok;
 }
 
-// Pass 1 (lean, high occupancy): the voxel that holds a vertex decides most triangles of a mesh finer than the voxels
-// with one table probe each and no SAT.  Undecided triangles go to a to-do list for pass 2.
-__global__ void __launch_bounds__(256, 4) mesh_vertex_probe_kernel(MapView m, double res, const double* __restrict__ verts,
-                                                                  unsigned long long nv, const int* __restrict__ faces4,
-                                                                  unsigned long long nt, uint8_t* __restrict__ flags,
-                                                                  unsigned int* __restrict__ todo,
-                                                                  unsigned int* __restrict__ todo_count)
+// ---- the mesh-mask kernels ---------------------------------------------------------------------------------------------------
+//
+// Measured on B200 (ncu, round 1 and 2): deciding a triangle is bound by instruction issue (address arithmetic, double
+// precision key arithmetic, hash probes), not by HBM traffic or latency.  Most of that work is per VERTEX, and a vertex of
+// a welded mesh is shared by ~6 triangles, so it is done once per vertex:
+//
+//   mesh_vertex_kernel   one thread per vertex: the voxel that holds it (floor estimate, validated with the exact closed
+//                        bounds), whether it lies exactly on that voxel's lower / upper faces (then it also touches the
+//                        neighbour), and whether that voxel is occupied -> one 8-byte record
+//   mesh_tri_kernel      one thread per triangle: the face and its three records.  Any vertex in an occupied voxel is a
+//                        contact.  Otherwise the exact key box of the triangle follows from the records alone
+//                        (min / max of the vertex keys, widened where a vertex sits on a face -- this equals key_range()
+//                        on the coordinates, see vertex_record()); its voxels other than the three vertex voxels (known to
+//                        be empty) are probed, and only if one of them is occupied are the nine coordinates fetched for the
+//                        closed separating-axis test.  For a mesh finer than the voxels there is usually nothing left to
+//                        probe.  Key boxes of 28 .. 4096 voxels are walked by the whole warp, larger ones go to
+//                        mesh_contacts_big_kernel (voxel-major).  Triangles with an unusable record (coordinate outside
+//                        the key range, estimate not validated) take the coordinate path (key_range()).
+constexpr unsigned long long kRecValid = 1ull << 48;      // key bits usable: finite, inside the key range, bounds validated
+constexpr unsigned long long kRecNonFinite = 1ull << 49;  // a non-finite coordinate: the triangle touches nothing
+constexpr unsigned long long kRecOccupied = 1ull << 50;   // the holding voxel has count1 >= 1
+constexpr int kRecOnLowShift = 51;                        // bits 51..53: coordinate == lower bound of the voxel (x, y, z)
+constexpr int kRecOnHighShift = 54;                       // bits 54..56: coordinate == upper bound
+
+__device__ __forceinline__ bool finite_d(double x) { return ((unsigned int)__double2hiint(x) & 0x7ff00000u) != 0x7ff00000u; }
+
+// Record of one vertex.  With k validated (vox_lo(k) <= x <= vox_hi(k)) the exact key interval of key_range() for the point
+// interval [x, x] is [k - (x == vox_lo(k)), k + (x == vox_hi(k))]: vox_hi(k - 1) and vox_lo(k) are the same expression, so
+// the voxel below qualifies iff x equals the shared bound, and likewise above.  key_range() is monotone in its arguments,
+// hence a triangle's interval is [min over vertices of the lower ends, max over vertices of the upper ends].
+__device__ __forceinline__ unsigned long long vertex_record(const MapView& m, double res, double x, double y, double z)
 {
-  const unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= nt)
-    return;
-  const int4 f = __ldg(reinterpret_cast<const int4*>(faces4) + t);
-  const bool ok = f.y >= 0 && f.z >= 0 && f.w >= 0 && (unsigned long long)f.y < nv && (unsigned long long)f.z < nv &&
-                  (unsigned long long)f.w < nv;
-  uint8_t flag = 0;
-  if (ok)
+  if (!(finite_d(x) && finite_d(y) && finite_d(z)))
+    return kRecNonFinite;
+  const double c[3] = { x, y, z };
+  unsigned long long rec = kRecValid;
+#pragma unroll
+  for (int ax = 0; ax < 3; ax++)
   {
-    const int idx[3] = { f.y, f.z, f.w };
-    double v[3][3];
-    bool finite = true;
-#pragma unroll
-    for (int i = 0; i < 3; i++)
-#pragma unroll
-      for (int a = 0; a < 3; a++)
-      {
-        v[i][a] = __ldg(verts + 3ull * idx[i] + a);
-        finite = finite && isfinite(v[i][a]);
-      }
-    // one vertex after the other, stopping at the first hit (for a mesh finer than the voxels that is vertex 0)
-    for (int i = 0; i < 3 && !flag; i++)
-    {
-      unsigned long long key = 0;
-      bool inside = true;
-#pragma unroll
-      for (int a = 0; a < 3; a++)
-      {
-        // e is integral, so e * res and (e + 1) * res are exactly the voxel's bounds (k - 32768) * res, (k - 32767) * res
-        const double e = fmin(fmax(floor(v[i][a] * m.inv_res), -32768.0), 32767.0);
-        inside = inside && v[i][a] >= e * res && v[i][a] <= (e + 1.0) * res;  // exact test guards the estimate
-        key |= (unsigned long long)((int)e + 32768) << (16 * a);
-      }
-      if (inside && map_occupied(m, key))
-        flag = 1;
-    }
-    if (!finite)
-      flag = 0;  // a triangle with a non-finite vertex touches nothing (same rule as the key-range walk)
-    else if (!flag)
-      todo[atomicAdd(todo_count, 1u)] = (unsigned int)t;
+    const int k = __double2int_rd(__dmul_rn(m.inv_res, c[ax])) + 32768;  // saturating conversion: far values land outside
+    if (k < 0 || k > 65535)
+      return 0ull;  // outside the key range: no record, coordinate path
+    const double lo = vox_lo(k, res), hi = vox_hi(k, res);
+    if (!(c[ax] >= lo && c[ax] <= hi))
+      return 0ull;  // the estimate is one voxel off (rounding of inv_res * x): coordinate path
+    rec |= (unsigned long long)(unsigned int)k << (16 * ax);
+    rec |= (unsigned long long)(c[ax] == lo) << (kRecOnLowShift + ax);
+    rec |= (unsigned long long)(c[ax] == hi) << (kRecOnHighShift + ax);
   }
-  flags[t] = flag;
+  if (map_occupied(m, rec & 0xffffffffffffull))
+    rec |= kRecOccupied;
+  return rec;
 }
 
-// Pass 2: triangles the vertex probe could not decide walk the voxel keys their bounding box covers and run the closed
-// separating-axis test against the occupied ones.
-__global__ void __launch_bounds__(128) mesh_contacts_kernel(MapView m, double res, const double* __restrict__ verts,
-                                                           unsigned long long nv, const int* __restrict__ faces4,
-                                                           uint8_t* __restrict__ flags, const unsigned int* __restrict__ todo,
-                                                           const unsigned int* __restrict__ todo_count,
-                                                           unsigned int* __restrict__ big_list,
-                                                           unsigned int* __restrict__ big_count)
+constexpr int kVertPerThread = 2;  // vertices per thread of mesh_vertex_kernel (loads and probes of both in flight)
+
+__global__ void __launch_bounds__(256) mesh_vertex_kernel(MapView m, double res, const double* __restrict__ verts,
+                                                         unsigned long long nv, unsigned long long* __restrict__ recs,
+                                                         unsigned int* __restrict__ counters)
+{
+  const unsigned long long i0 = (unsigned long long)blockIdx.x * (blockDim.x * kVertPerThread) + threadIdx.x;
+  if (i0 == 0)
+    counters[0] = counters[1] = 0u;  // to-do and big-triangle counts of this call (first kernel of the call, stream order)
+  double c[kVertPerThread][3];
+#pragma unroll
+  for (int j = 0; j < kVertPerThread; j++)
+  {
+    const unsigned long long i = i0 + (unsigned long long)j * blockDim.x;
+#pragma unroll
+    for (int ax = 0; ax < 3; ax++)
+      c[j][ax] = i < nv ? __ldg(verts + 3ull * i + ax) : 0.0;
+  }
+#pragma unroll
+  for (int j = 0; j < kVertPerThread; j++)
+  {
+    const unsigned long long i = i0 + (unsigned long long)j * blockDim.x;
+    const unsigned long long rec = vertex_record(m, res, c[j][0], c[j][1], c[j][2]);
+    if (i < nv)
+      recs[i] = rec;
+  }
+}
+
+__device__ __forceinline__ bool face_ok(const int4& f, unsigned long long nv)
+{
+  return f.y >= 0 && f.z >= 0 && f.w >= 0 && (unsigned long long)f.y < nv && (unsigned long long)f.z < nv &&
+         (unsigned long long)f.w < nv;
+}
+
+__device__ __forceinline__ bool voxel_hits_tri(double res, int kx, int ky, int kz, const double* v0, const double* v1,
+                                               const double* v2)
+{
+  const double blo[3] = { vox_lo(kx, res), vox_lo(ky, res), vox_lo(kz, res) };
+  const double bhi[3] = { vox_hi(kx, res), vox_hi(ky, res), vox_hi(kz, res) };
+  return tri_box_overlap(blo, bhi, v0, v1, v2);
+}
+
+__device__ __forceinline__ void load_verts(const double* __restrict__ verts, const int4& f, double* v0, double* v1, double* v2)
+{
+#pragma unroll
+  for (int ax = 0; ax < 3; ax++)
+  {
+    v0[ax] = __ldg(verts + 3ull * f.y + ax);
+    v1[ax] = __ldg(verts + 3ull * f.z + ax);
+    v2[ax] = __ldg(verts + 3ull * f.w + ax);
+  }
+}
+
+constexpr int kSmallBoxLimit = 27;  // voxels one thread probes on its own
+constexpr int kTriPerThread = 4;    // triangles per thread of mesh_tri_kernel: their loads are issued together
+
+// exact key box of a triangle from its three (valid) records: lower corner and extent per axis
+__device__ __forceinline__ void box_from_records(unsigned long long r0, unsigned long long r1, unsigned long long r2, int* lo, int* n)
+{
+#pragma unroll
+  for (int ax = 0; ax < 3; ax++)
+  {
+    const int k0 = (int)((r0 >> (16 * ax)) & 0xffffull), k1 = (int)((r1 >> (16 * ax)) & 0xffffull),
+              k2 = (int)((r2 >> (16 * ax)) & 0xffffull);
+    const int l0 = k0 - (int)((r0 >> (kRecOnLowShift + ax)) & 1ull), l1 = k1 - (int)((r1 >> (kRecOnLowShift + ax)) & 1ull),
+              l2 = k2 - (int)((r2 >> (kRecOnLowShift + ax)) & 1ull);
+    const int h0 = k0 + (int)((r0 >> (kRecOnHighShift + ax)) & 1ull), h1 = k1 + (int)((r1 >> (kRecOnHighShift + ax)) & 1ull),
+              h2 = k2 + (int)((r2 >> (kRecOnHighShift + ax)) & 1ull);
+    lo[ax] = max(min(min(l0, l1), l2), 0);
+    n[ax] = min(max(max(h0, h1), h2), 65535) - lo[ax] + 1;
+  }
+}
+
+// Common path: one thread takes 4 triangles and issues their 4 face loads, then their 12 record loads, together.
+//   * a vertex inside an occupied voxel                                   -> contact
+//   * no such vertex, and the key box consists of the vertex voxels only  -> no contact (those voxels are known to be empty;
+//     this is the usual case for a mesh finer than the voxels)
+//   * anything else (other voxels to probe, unusable record)              -> to-do list of mesh_undecided_kernel, appended
+//     with one atomic per CTA; the flag is written 0 here and overwritten there on contact.
+// The kernel makes no calls and holds no coordinates, so it stays small in registers and code.
+__global__ void __launch_bounds__(256, 4) mesh_tri_kernel(const double* __restrict__ verts, unsigned long long nv,
+                                                         const int* __restrict__ faces4, unsigned long long nt,
+                                                         const unsigned long long* __restrict__ recs,
+                                                         uint8_t* __restrict__ flags, unsigned int* __restrict__ todo,
+                                                         unsigned int* __restrict__ todo_count)
+{
+  __shared__ unsigned int s_warp_count[8], s_base;
+  const unsigned int lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const unsigned long long t0 = (unsigned long long)blockIdx.x * (blockDim.x * kTriPerThread) + threadIdx.x;
+  int4 f[kTriPerThread];
+#pragma unroll
+  for (int j = 0; j < kTriPerThread; j++)
+  {
+    const unsigned long long t = t0 + (unsigned long long)j * blockDim.x;
+    f[j] = make_int4(0, -1, -1, -1);
+    if (t < nt)
+      f[j] = __ldg(reinterpret_cast<const int4*>(faces4) + t);
+  }
+  unsigned long long r[kTriPerThread][3];
+#pragma unroll
+  for (int j = 0; j < kTriPerThread; j++)
+  {
+    r[j][0] = r[j][1] = r[j][2] = kRecNonFinite;  // invalid faces and the padding beyond nt touch nothing
+    if (face_ok(f[j], nv))
+    {
+      r[j][0] = __ldg(recs + f[j].y);
+      r[j][1] = __ldg(recs + f[j].z);
+      r[j][2] = __ldg(recs + f[j].w);
+    }
+  }
+  unsigned int und_mask = 0;  // bit j: triangle j of this thread goes to the to-do list
+#pragma unroll
+  for (int j = 0; j < kTriPerThread; j++)
+  {
+    const unsigned long long t = t0 + (unsigned long long)j * blockDim.x;
+    const unsigned long long any = r[j][0] | r[j][1] | r[j][2], all = r[j][0] & r[j][1] & r[j][2];
+    const bool finite = !(any & kRecNonFinite);  // a triangle with a non-finite vertex touches nothing
+    const bool hit = finite && (all & kRecValid) && (any & kRecOccupied);  // a vertex inside an occupied voxel
+    bool undecided = finite && !hit;
+    if (undecided && (all & kRecValid))
+    {
+      int lo[3], n[3];
+      box_from_records(r[j][0], r[j][1], r[j][2], lo, n);
+      const unsigned long long kmask = 0xffffffffffffull;
+      const unsigned long long k0 = r[j][0] & kmask, k1 = r[j][1] & kmask, k2 = r[j][2] & kmask;
+      const int distinct = 1 + (k1 != k0 ? 1 : 0) + ((k2 != k0 && k2 != k1) ? 1 : 0);
+      // the vertex voxels lie inside the box, so the box holds nothing else iff its volume equals their number
+      if (n[0] * n[1] * n[2] == distinct && n[0] <= 3 && n[1] <= 3 && n[2] <= 3)
+        undecided = false;
+    }
+    und_mask |= undecided ? (1u << j) : 0u;
+    if (t < nt)
+      flags[t] = hit ? 1 : 0;
+  }
+  // one to-do slot range per CTA
+  const unsigned int mine = (unsigned int)__popc(und_mask);
+  unsigned int incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1)
+  {
+    const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= (unsigned int)o)
+      incl += v;
+  }
+  if (lane == 31)
+    s_warp_count[warp] = incl;
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    unsigned int total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++)
+    {
+      const unsigned int c = s_warp_count[w];
+      s_warp_count[w] = total;
+      total += c;
+    }
+    s_base = total ? atomicAdd(todo_count, total) : 0u;
+  }
+  __syncthreads();
+  unsigned int dst = s_base + s_warp_count[warp] + incl - mine;
+#pragma unroll
+  for (int j = 0; j < kTriPerThread; j++)
+    if (und_mask & (1u << j))
+      todo[dst++] = (unsigned int)(t0 + (unsigned long long)j * blockDim.x);
+}
+
+// The undecided triangles (no vertex in an occupied voxel): exact key box from the records (or from the coordinates
+// when a record is unusable), probes of the box voxels other than the vertex voxels, closed separating-axis test where
+// one is occupied.  A warp takes 32 consecutive to-do entries so that key boxes of 28 .. 4096 voxels can be walked by the
+// whole warp; larger ones go to the big list.
+__global__ void __launch_bounds__(128) mesh_undecided_kernel(const MapView m, double res, const double* __restrict__ verts,
+                                                            const int* __restrict__ faces4,
+                                                            const unsigned long long* __restrict__ recs,
+                                                            uint8_t* __restrict__ flags, const unsigned int* __restrict__ todo,
+                                                            const unsigned int* __restrict__ todo_count,
+                                                            unsigned int* __restrict__ big_list,
+                                                            unsigned int* __restrict__ big_count)
 {
   const unsigned int n_todo = *todo_count;
-  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_todo; i += gridDim.x * blockDim.x)
+  const unsigned int lane = threadIdx.x & 31u;
+  const unsigned int n_round = (n_todo + 31u) & ~31u;  // whole warps stay converged for the ballots
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x)
   {
-    const unsigned long long t = todo[i];
-    TriData d;
-    load_tri(verts, nv, faces4, t, res, m.inv_res, d);
-    if (!d.ok)
-      continue;
-    const unsigned long long vol = (unsigned long long)(d.hi[0] - d.lo[0] + 1) * (unsigned long long)(d.hi[1] - d.lo[1] + 1) *
-                                   (unsigned long long)(d.hi[2] - d.lo[2] + 1);
-    if (vol > kInlineRangeLimit)
+    const bool live = i < n_todo;
+    unsigned int t = 0;
+    int4 f = make_int4(3, 0, 0, 0);
+    unsigned long long r0 = 0ull, r1 = 0ull, r2 = 0ull;
+    if (live)
     {
-      big_list[atomicAdd(big_count, 1u)] = (unsigned int)t;  // handled voxel-major by mesh_contacts_big_kernel
-      continue;
+      t = todo[i];
+      f = __ldg(reinterpret_cast<const int4*>(faces4) + t);
+      r0 = __ldg(recs + f.y);
+      r1 = __ldg(recs + f.z);
+      r2 = __ldg(recs + f.w);
     }
+    const unsigned long long all = r0 & r1 & r2;
+    int lo[3] = { 0, 0, 0 }, n[3] = { 0, 0, 0 };
+    bool range_ok = live, have_verts = false, medium = false;
     uint8_t flag = 0;
-    for (int kz = d.lo[2]; kz <= d.hi[2] && !flag; kz++)
-      for (int ky = d.lo[1]; ky <= d.hi[1] && !flag; ky++)
-        for (int kx = d.lo[0]; kx <= d.hi[0] && !flag; kx++)
+    double v0[3], v1[3], v2[3];
+    if (live)
+    {
+      if (all & kRecValid)
+      {
+        box_from_records(r0, r1, r2, lo, n);  // exact key box from the records
+      }
+      else
+      {
+        // coordinate path: a vertex outside the key range or with an unvalidated estimate
+        load_verts(verts, f, v0, v1, v2);
+        have_verts = true;
+#pragma unroll
+        for (int ax = 0; ax < 3; ax++)
         {
-          const unsigned long long key = ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | (unsigned long long)kx;
-          if (!map_occupied(m, key))
-            continue;
-          const double blo[3] = { vox_lo(kx, res), vox_lo(ky, res), vox_lo(kz, res) };
-          const double bhi[3] = { vox_hi(kx, res), vox_hi(ky, res), vox_hi(kz, res) };
-          if (tri_box_overlap(blo, bhi, d.v0, d.v1, d.v2))
-            flag = 1;
+          int hi;
+          range_ok = key_range(dmin3(v0[ax], v1[ax], v2[ax]), dmax3(v0[ax], v1[ax], v2[ax]), res, m.inv_res, lo[ax], hi) && range_ok;
+          n[ax] = hi - lo[ax] + 1;
         }
-    if (flag)
+      }
+    }
+    if (range_ok)
+    {
+      const unsigned long long vol = (unsigned long long)n[0] * (unsigned long long)n[1] * (unsigned long long)n[2];
+      if (vol > kInlineRangeLimit)
+        big_list[atomicAdd(big_count, 1u)] = t;  // handled voxel-major by mesh_contacts_big_kernel
+      else if (vol > (unsigned long long)kSmallBoxLimit)
+        medium = true;
+      else
+      {
+        // the vertex voxels are known to be empty when all three records are valid: only the other voxels are probed
+        const unsigned long long kmask = 0xffffffffffffull;
+        const bool skip = (all & kRecValid) != 0ull;
+        for (int dz = 0; dz < n[2] && !flag; dz++)
+          for (int dy = 0; dy < n[1] && !flag; dy++)
+            for (int dx = 0; dx < n[0] && !flag; dx++)
+            {
+              const int kx = lo[0] + dx, ky = lo[1] + dy, kz = lo[2] + dz;
+              const unsigned long long key = ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | (unsigned long long)kx;
+              if (skip && (key == (r0 & kmask) || key == (r1 & kmask) || key == (r2 & kmask)))
+                continue;
+              if (!map_occupied(m, key))
+                continue;
+              if (!have_verts)
+              {
+                load_verts(verts, f, v0, v1, v2);
+                have_verts = true;
+              }
+              if (voxel_hits_tri(res, kx, ky, kz, v0, v1, v2))
+                flag = 1;
+            }
+      }
+    }
+    // key boxes of 28 .. 4096 voxels: the warp walks them together, 32 voxels per step
+    unsigned int walk = __ballot_sync(0xffffffffu, medium);
+    while (walk)
+    {
+      const int src = __ffs(walk) - 1;
+      walk &= walk - 1;
+      int4 fs;
+      fs.x = 3;
+      fs.y = __shfl_sync(0xffffffffu, f.y, src);
+      fs.z = __shfl_sync(0xffffffffu, f.z, src);
+      fs.w = __shfl_sync(0xffffffffu, f.w, src);
+      const int bx = __shfl_sync(0xffffffffu, lo[0], src), by = __shfl_sync(0xffffffffu, lo[1], src),
+                bz = __shfl_sync(0xffffffffu, lo[2], src);
+      const int nx = __shfl_sync(0xffffffffu, n[0], src), ny = __shfl_sync(0xffffffffu, n[1], src),
+                nz = __shfl_sync(0xffffffffu, n[2], src);
+      double w0[3], w1[3], w2[3];
+      load_verts(verts, fs, w0, w1, w2);
+      const unsigned int vol = (unsigned int)(nx * ny * nz);
+      bool hit = false;
+      for (unsigned int base = 0; base < vol && !hit; base += 32)
+      {
+        const unsigned int q = base + lane;
+        bool mine = false;
+        if (q < vol)
+        {
+          const int kx = bx + (int)(q % (unsigned int)nx), ky = by + (int)((q / (unsigned int)nx) % (unsigned int)ny),
+                    kz = bz + (int)(q / (unsigned int)(nx * ny));
+          const unsigned long long key48 = ((unsigned long long)kz << 32) | ((unsigned long long)ky << 16) | (unsigned long long)kx;
+          mine = map_occupied(m, key48) && voxel_hits_tri(res, kx, ky, kz, w0, w1, w2);
+        }
+        hit = __any_sync(0xffffffffu, mine);
+      }
+      if ((int)lane == src && hit)
+        flag = 1;
+    }
+    if (live && flag)
       flags[t] = 1;
   }
 }
@@ -279,28 +532,29 @@ __global__ void __launch_bounds__(256) mesh_contacts_big_kernel(MapView m, doubl
                                                                const unsigned int* __restrict__ big_count)
 {
   const unsigned int n_big = *big_count;
-  if (n_big == 0)
-    return;
-  const unsigned long long n_slots = m.mask + 1;
-  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots;
-       i += (unsigned long long)gridDim.x * blockDim.x)
+  if (n_big != 0)
   {
-    const Slot s = m.slots[i];
-    if (s.key == 0ull || (s.counts >> 32) == 0ull)
-      continue;
-    const unsigned long long k = s.key & ~kValidBit;
-    const int kx = (int)(k & 0xffff), ky = (int)((k >> 16) & 0xffff), kz = (int)((k >> 32) & 0xffff);
-    const double blo[3] = { vox_lo(kx, res), vox_lo(ky, res), vox_lo(kz, res) };
-    const double bhi[3] = { vox_hi(kx, res), vox_hi(ky, res), vox_hi(kz, res) };
-    for (unsigned int b = 0; b < n_big; b++)
+    const unsigned long long n_slots = m.mask + 1;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots;
+         i += (unsigned long long)gridDim.x * blockDim.x)
     {
-      const unsigned int t = big_list[b];
-      if (flags[t])
+      const Slot s = m.slots[i];
+      if (s.key == 0ull || (s.counts >> 32) == 0ull)
         continue;
-      TriData d;
-      load_tri(verts, nv, faces4, t, res, m.inv_res, d);
-      if (d.ok && tri_box_overlap(blo, bhi, d.v0, d.v1, d.v2))
-        flags[t] = 1;
+      const unsigned long long k = s.key & ~kValidBit;
+      const int kx = (int)(k & 0xffff), ky = (int)((k >> 16) & 0xffff), kz = (int)((k >> 32) & 0xffff);
+      const double blo[3] = { vox_lo(kx, res), vox_lo(ky, res), vox_lo(kz, res) };
+      const double bhi[3] = { vox_hi(kx, res), vox_hi(ky, res), vox_hi(kz, res) };
+      for (unsigned int b = 0; b < n_big; b++)
+      {
+        const unsigned int t = big_list[b];
+        if (flags[t])
+          continue;
+        TriData d;
+        load_tri(verts, nv, faces4, t, res, m.inv_res, d);
+        if (d.ok && tri_box_overlap(blo, bhi, d.v0, d.v1, d.v2))
+          flags[t] = 1;
+      }
     }
   }
 }
@@ -378,29 +632,38 @@ __global__ void colorize_kernel(const uint8_t* __restrict__ flags, const int* __
 int mesh_contacts_launch(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev,
                          uint64_t nt, uint8_t* flags_dev)
 {
-  // scratch: [todo_count, big_count (16 B)] [todo list: nt u32] [big list: nt u32]
+  // Two counters ([0] to-do, [1] big triangles) in a small context-owned buffer; mesh_vertex_kernel, the first kernel of a
+  // call, zeroes them, so no memset is launched.  The to-do list, the big list (nt u32 each) and the vertex records
+  // (nv u64) are ordinary scratch.
+  if (!ctx->mesh_counters)
+    PCS_CUDA(cudaMalloc(&ctx->mesh_counters, 64));
+  auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+  const size_t list_bytes = al(nt * sizeof(unsigned int));
   void* scr = nullptr;
-  PCS_TRY(ctx_scratch(ctx, 16 + 2 * nt * sizeof(unsigned int), &scr));
-  unsigned int* todo_count = (unsigned int*)scr;
-  unsigned int* big_count = todo_count + 1;
-  unsigned int* todo = (unsigned int*)((char*)scr + 16);
-  unsigned int* big_list = todo + nt;
-  PCS_CUDA(cudaMemsetAsync(scr, 0, 16, ctx->stream));
-  const unsigned long long mx = (unsigned long long)ctx->sm_count * 8ull;
-  mesh_vertex_probe_kernel<<<(unsigned int)((nt + 255) / 256), 256, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv,
-                                                                                     faces4_dev, nt, flags_dev, todo, todo_count);
+  PCS_TRY(ctx_scratch(ctx, 2 * list_bytes + nv * sizeof(unsigned long long) + 16, &scr));
+  unsigned int* counters = (unsigned int*)ctx->mesh_counters;
+  unsigned int* todo = (unsigned int*)scr;
+  unsigned int* big_list = (unsigned int*)((char*)scr + list_bytes);
+  unsigned long long* recs = (unsigned long long*)((char*)scr + 2 * list_bytes);
+  const unsigned int mx = (unsigned int)ctx->sm_count * 8u;
+
+  mesh_vertex_kernel<<<(unsigned int)((nv + 256 * kVertPerThread - 1) / (256 * kVertPerThread)) + (nv == 0 ? 1u : 0u), 256, 0,
+                       ctx->stream>>>(map->view, map->resolution,
+                                                                                                  verts_dev, nv, recs, counters);
+  mesh_tri_kernel<<<(unsigned int)((nt + 256 * kTriPerThread - 1) / (256 * kTriPerThread)), 256, 0, ctx->stream>>>(
+      verts_dev, nv, faces4_dev, nt, recs, flags_dev, todo, counters);
   unsigned long long blocks = (nt + 127) / 128;
   if (blocks > mx)
     blocks = mx;
-  mesh_contacts_kernel<<<(unsigned int)blocks, 128, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv, faces4_dev,
-                                                                    flags_dev, todo, todo_count, big_list, big_count);
+  mesh_undecided_kernel<<<(unsigned int)blocks, 128, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, faces4_dev, recs,
+                                                                      flags_dev, todo, counters, big_list, counters + 1);
   blocks = (map->n_slots + 255) / 256;
-  if (blocks > mx)
-    blocks = mx;
+  if (blocks > (unsigned long long)ctx->sm_count * 4ull)
+    blocks = (unsigned long long)ctx->sm_count * 4ull;
   mesh_contacts_big_kernel<<<(unsigned int)blocks, 256, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv, faces4_dev,
-                                                                        flags_dev, big_list, big_count);
-  count_launch(ctx, 3);
-  return check_launch("mesh_contacts_kernel");
+                                                                        flags_dev, big_list, counters + 1);
+  count_launch(ctx, 4);
+  return check_launch("mesh_tri_kernel");
 }
 }  // namespace pcs
 
@@ -419,6 +682,78 @@ int pcs_mesh_contacts_dev(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, u
   PCS_CHECK_ARG(verts_dev && faces4_dev && tri_flags_dev, "NULL argument");
   PCS_CHECK_ARG(((uintptr_t)faces4_dev & 15u) == 0, "faces4 must be 16-byte aligned");
   return mesh_contacts_launch(ctx, map, verts_dev, nv, faces4_dev, nt, tri_flags_dev);
+}
+
+// device-resident mask assembly shared by pcs_mesh_mask and pcs_mesh_mask_dev: flags -> compacted INSIDE / OUTSIDE
+// triangles, or per-vertex colours.  *d_total_out points at the device-side count of kept triangles (compaction modes).
+static int mesh_assemble_dev(pcs_ctx* ctx, const double* d_verts, uint64_t nv, const int32_t* d_faces, uint64_t nt,
+                             const uint8_t* d_flags, int mask_type, uint64_t cap, double* d_ov, int32_t* d_of, uint8_t* d_orgb,
+                             const unsigned long long** d_total_out)
+{
+  *d_total_out = nullptr;
+  if (mask_type == PCS_RETURN_COLORIZED)
+  {
+    if (d_orgb && nv)
+    {
+      fill_rgb_kernel<<<(unsigned int)((nv + 255) / 256), 256, 0, ctx->stream>>>(d_orgb, nv);
+      if (nt)
+        colorize_kernel<<<(unsigned int)((nt + 255) / 256), 256, 0, ctx->stream>>>(d_flags, d_faces, nt, nv, d_orgb);
+      count_launch(ctx, nt ? 2 : 1);
+      PCS_TRY(check_launch("colorize_kernel"));
+    }
+    return PCS_OK;
+  }
+  if (nt == 0)
+    return PCS_OK;
+  void* scr = nullptr;
+  // the contact kernels are done with the scratch (stream order), so the compaction can reuse it
+  PCS_TRY(ctx_scratch(ctx, compact_scratch_bytes(nt), &scr));
+  FlagPred pred{ d_flags, (uint8_t)(mask_type == PCS_RETURN_INSIDE ? 1 : 0) };
+  if (d_ov && d_of && d_orgb)
+  {
+    TriEmit emit{ d_verts, d_faces, d_ov, d_of, d_orgb, cap };
+    PCS_TRY(compact_run(ctx, pred, emit, nt, scr, d_total_out));
+  }
+  else
+    PCS_TRY(compact_run(ctx, pred, NullEmit{}, nt, scr, d_total_out));
+  return PCS_OK;
+}
+
+int pcs_mesh_mask_dev(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev, uint64_t nt,
+                      int mask_type, uint64_t out_cap_tris, double* out_verts_dev, int32_t* out_faces4_dev,
+                      uint8_t* out_rgb_dev, uint8_t* tri_flags_dev, uint64_t* n_out_tris_dev)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(map != nullptr, "octree / map not set");
+  PCS_CHECK_ARG(mask_type >= 0 && mask_type <= 2, "Invalid mask type");
+  PCS_CHECK_ARG(nt < (1ull << 31) && nv < (1ull << 31), "mesh too large");
+  PCS_CHECK_ARG(tri_flags_dev != nullptr || nt == 0, "tri_flags_dev is NULL");
+  PCS_CHECK_ARG(((uintptr_t)faces4_dev & 15u) == 0 && ((uintptr_t)out_faces4_dev & 15u) == 0, "faces4 must be 16-byte aligned");
+  PCS_CHECK_ARG(((uintptr_t)n_out_tris_dev & 7u) == 0, "n_out_tris_dev must be 8-byte aligned");
+  if (nt)
+  {
+    PCS_CHECK_ARG(verts_dev && faces4_dev, "input mesh not set");
+    PCS_TRY(mesh_contacts_launch(ctx, map, verts_dev, nv, faces4_dev, nt, tri_flags_dev));
+  }
+  const unsigned long long* d_total = nullptr;
+  PCS_TRY(mesh_assemble_dev(ctx, verts_dev, nv, faces4_dev, nt, tri_flags_dev, mask_type, out_cap_tris, out_verts_dev,
+                            out_faces4_dev, out_rgb_dev, &d_total));
+  if (n_out_tris_dev)
+  {
+    if (d_total)
+      PCS_CUDA(cudaMemcpyAsync(n_out_tris_dev, d_total, 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    else
+    {
+      // COLORIZED keeps every triangle; an empty mesh keeps none
+      void* h = nullptr;
+      PCS_TRY(ctx_pinned(ctx, 64, &h));
+      PCS_CUDA(cudaStreamSynchronize(ctx->stream));  // the pinned word may still be in use by an earlier copy
+      *(unsigned long long*)((char*)h + 32) = (mask_type == PCS_RETURN_COLORIZED) ? nt : 0ull;
+      PCS_CUDA(cudaMemcpyAsync(n_out_tris_dev, (char*)h + 32, 8, cudaMemcpyHostToDevice, ctx->stream));
+      PCS_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+  }
+  return PCS_OK;
 }
 
 int pcs_mesh_mask(pcs_ctx* ctx, pcs_map* map, const double* verts, uint64_t nv, const int32_t* faces4, uint64_t nt,
@@ -473,11 +808,8 @@ int pcs_mesh_mask(pcs_ctx* ctx, pcs_map* map, const double* verts, uint64_t nv, 
       {
         void* d_rgb = nullptr;
         PCS_TRY(ctx_staging(ctx, 1, (size_t)nv * 3, &d_rgb));
-        fill_rgb_kernel<<<(unsigned int)((nv + 255) / 256), 256, 0, ctx->stream>>>((uint8_t*)d_rgb, nv);
-        if (nt)
-          colorize_kernel<<<(unsigned int)((nt + 255) / 256), 256, 0, ctx->stream>>>(d_flags, d_faces, nt, nv, (uint8_t*)d_rgb);
-        count_launch(ctx, nt ? 2 : 1);
-        PCS_TRY(check_launch("colorize_kernel"));
+        const unsigned long long* unused = nullptr;
+        PCS_TRY(mesh_assemble_dev(ctx, d_verts, nv, d_faces, nt, d_flags, mask_type, nt, nullptr, nullptr, (uint8_t*)d_rgb, &unused));
         PCS_CUDA(cudaMemcpyAsync(out_rgb, d_rgb, (size_t)nv * 3, cudaMemcpyDeviceToHost, ctx->stream));
         ctx->stats.bytes_d2h += (size_t)nv * 3;
       }
@@ -500,25 +832,16 @@ int pcs_mesh_mask(pcs_ctx* ctx, pcs_map* map, const double* verts, uint64_t nv, 
   }
   const bool emit_now = out_verts && out_faces4 && out_rgb;
   const uint64_t cap = emit_now ? (out_cap_tris < nt ? out_cap_tris : nt) : 0;
-  void *scr = nullptr, *d_out = nullptr, *h_total = nullptr;
+  void *d_out = nullptr, *h_total = nullptr;
   PCS_TRY(ctx_pinned(ctx, 64, &h_total));
-  const size_t scr_bytes = compact_scratch_bytes(nt);
-  // the contact kernels are done with the scratch (stream order), so the compaction can reuse it
-  PCS_TRY(ctx_scratch(ctx, scr_bytes, &scr));
   const size_t ov = (size_t)cap * 72, of = (size_t)cap * 16, orgb = (size_t)cap * 9;
   PCS_TRY(ctx_staging(ctx, 1, ((ov + 255) & ~(size_t)255) + ((of + 255) & ~(size_t)255) + orgb + 256, &d_out));
   double* d_ov = (double*)d_out;
   int32_t* d_of = (int32_t*)((char*)d_out + ((ov + 255) & ~(size_t)255));
   uint8_t* d_orgb = (uint8_t*)d_of + ((of + 255) & ~(size_t)255);
-  FlagPred pred{ d_flags, (uint8_t)(mask_type == PCS_RETURN_INSIDE ? 1 : 0) };
   const unsigned long long* d_total = nullptr;
-  if (emit_now)
-  {
-    TriEmit emit{ d_verts, d_faces, d_ov, d_of, d_orgb, cap };
-    PCS_TRY(compact_run(ctx, pred, emit, nt, scr, &d_total));
-  }
-  else
-    PCS_TRY(compact_run(ctx, pred, NullEmit{}, nt, scr, &d_total));
+  PCS_TRY(mesh_assemble_dev(ctx, d_verts, nv, d_faces, nt, d_flags, mask_type, cap, emit_now ? d_ov : nullptr,
+                            emit_now ? d_of : nullptr, emit_now ? d_orgb : nullptr, &d_total));
   PCS_CUDA(cudaMemcpyAsync(h_total, d_total, 8, cudaMemcpyDeviceToHost, ctx->stream));
   PCS_CUDA(cudaStreamSynchronize(ctx->stream));
   const uint64_t kept = *(const unsigned long long*)h_total;
