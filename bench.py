@@ -9,8 +9,14 @@ pcs_synth_frames_dev before the timed region; the scan (8.8 GB) is far larger th
 Timing is by CUDA events on the stream the kernels run on, bracketed by a barrier + synchronize, max over ranks.
 
 For N > 1 (launched by torch.distributed.run) every rank owns a frame shard and a local voxel map; inside the timed
-step the local maps are packed by owner (mix64(key48) % N), exchanged with one NCCL all-to-all and merged into the
-owned slices ("scaling": "weak").
+step every local voxel is pushed to its owner (mix64(key48) % N) by one kernel over NVLink peer memory (default,
+`--exchange peer`), or packed by owner, exchanged with one NCCL all-to-all and merged (`--exchange nccl`)
+("scaling": "weak").  After the timed region the exchanged map is checked against one GPU integrating the whole
+N-shard scan (`exchange_check`).
+
+The same line carries the other BASELINE.json configurations as sub-objects (`config1`: one 640x480 frame + 10 k-triangle
+mesh through the host API; `config5`: 3840x2160 frames at 2 mm with a voxel table larger than L2; `mesh_mask`: the 2 M
+triangle mesh at three surviving fractions; `detector`: the opening path), each with its own roofline.
 
 Prints ONE JSON line (rank 0).  `--impl reference` times the reference's CPU path instead (the oracle port: the
 reference itself cannot be compiled here) on the host cores.
@@ -40,6 +46,19 @@ WORKLOADS = {
     "scan16_3840x2160_2mm": (16, 3840, 2160, 0.002, 1 << 20),
 }
 DEFAULT_WORKLOAD = "scan300_1280x720_5mm"
+
+
+def make_config(workload: str, world: int, exchange_kind: str | None = "peer") -> dict:
+    """The `config` object of the JSON line; the GPU arm and the reference arm print the same one."""
+    frames_per_gpu, w, h, res, _ = WORKLOADS[workload]
+    partition = "single GPU"
+    if world > 1:
+        partition = ("frames sharded by rank, voxel owner = mix64(key48) % n_gpus, exchange = " +
+                     ("one push kernel over NVLink peer memory (CUDA IPC)" if exchange_kind == "peer"
+                      else "NCCL all-to-all of 16-byte records"))
+    return {"workload": workload, "frames_per_gpu": frames_per_gpu, "width": w, "height": h, "voxel_resolution_m": res,
+            "label_filter": "lower=255 upper=255", "outputs": "annotated cloud + mask + voxel map",
+            "l2": "inputs larger than L2 (no flush needed)", "partition": partition}
 
 
 def synth_pose(frame: int) -> np.ndarray:
@@ -154,13 +173,13 @@ def run_reference(args, rank, world):
     pts = n_sample * w * h
     ms = 1e3 * float(np.mean(times))
     value = pts / (ms * 1e-3)
-    sample = f"{n_sample} of {frames_per_gpu} frames {w}x{h} per step, annotate on {cores} threads, octree insert serial"
+    sample = (f"{n_sample} of the {frames_per_gpu} frames ({w}x{h}) per step, annotate on {cores} threads, octree insert "
+              f"serial; the rate is per point, so the sample size does not enter the value")
     line = {
         "impl": "reference", "metric": "annotated+integrated points/sec", "value": value, "unit": "points/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8+f32", "data": "synthetic",
-        "config": {"workload": args.workload, "frames_per_step": n_sample, "width": w, "height": h,
-                   "voxel_resolution_m": res, "label_filter": "lower=255 upper=255"},
+        "config": make_config(args.workload, max(world, args.gpus), args.exchange),
         "cpu_baseline": {"value": value, "unit": "points/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -185,6 +204,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mesh", action="store_true")
+    ap.add_argument("--no-config5", action="store_true")
+    ap.add_argument("--no-exchange-check", action="store_true")
+    ap.add_argument("--headline-only", action="store_true", help="skip the sub-objects (mesh, detector, config1, config5)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -328,10 +350,18 @@ def main():
     if not args.no_e2e:
         e2e = run_e2e(ctx, pcs, vmap, params, d_in, poses, frames_per_gpu, w, h, args, dist, torch, world, exch)
 
+    # The sections below run after the timed region; the headline map must be the result of the LAST TIMED step for the
+    # mesh, so the mesh goes first (the detector section re-integrates the same scan into it afterwards).
+    sub = not args.headline_only
     # ---- mesh mask on the aggregated map (BASELINE metric "mesh-mask tris/sec", config 4) -----------------------
     mesh = None
-    if not args.no_mesh and world == 1:
+    if sub and not args.no_mesh and world == 1:
         mesh = run_mesh(ctx, pcs, vmap, frames_per_gpu, peak)
+
+    # ---- the opening path (fused kernel with morph_open, image kernels): rank 0 ---------------------------------
+    detector = None
+    if sub and rank == 0:
+        detector = run_detector(ctx, pcs, vmap, params, d_in, d_pose, d_ann, d_mask, frames_per_gpu, w, h, peak, k_avg_ms)
 
     # ---- CPU baseline: the oracle port on a bounded sample of the same workload (rank 0, N = 1 only) ------------
     cpu = None
@@ -346,23 +376,42 @@ def main():
                "sample": f"first {n_s} of {frames_per_gpu} frames ({r['points']} points, {secs:.1f} s): "
                          f"annotate {r['seconds_annotate']:.2f} s, octree insert+prune {r['seconds_integrate']:.2f} s",
                "host_cpus": os.cpu_count()}
+        del host
+
+    # ---- BASELINE configs[0] (one frame + 10 k-triangle mesh, host API): rank 0 ------------------------------------
+    config1 = run_config1(ctx, pcs, peak) if (sub and rank == 0) else None
+
+    # ---- exchanged-map parity check (N > 1): last user of d_in / d_pose, which rank 0 overwrites ---------------------
+    exchange_check = None
+    if dist is not None and exch is not None and not args.no_exchange_check and not args.exchange_debug:
+        have = e2e is not None and e2e.get("finite_points") is not None and e2e.get("frames_per_step") == frames_per_gpu
+        t = torch.tensor([e2e["finite_points"] if have else 0, 1 if have else 0], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t)
+        finite_all = int(t[0].item()) if int(t[1].item()) == world else None  # only if every rank counted its whole shard
+        exchange_check = run_exchange_check(ctx, pcs, dist, torch, rank, world, exch, exchange_kind, vmap, params, d_in, d_pose,
+                                            frames_per_gpu, w, h, res, cap, finite_all)
+
+    # ---- BASELINE configs[4] (3840x2160 at 2 mm, table larger than L2) at every N: frees the headline buffers first ----
+    config5 = None
+    if sub and not args.no_config5:
+        for p_ in (d_in, d_ann, d_mask):
+            ctx.dev_free(p_)
+        config5 = run_config5(ctx, pcs, dist, torch, rank, world, peak, max(3, min(args.steps, 10)), True)
 
     if rank == 0:
         line = {
             "metric": "annotated+integrated points/sec", "value": value, "unit": "points/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8+f32", "data": "synthetic",
-            "config": {"workload": args.workload, "frames_per_gpu": frames_per_gpu, "width": w, "height": h,
-                       "voxel_resolution_m": res, "label_filter": "lower=255 upper=255",
-                       "outputs": "annotated cloud + mask + voxel map", "l2": "inputs larger than L2 (no flush needed)",
-                       "partition": ("frames sharded by rank, voxel owner = mix64(key48) % n_gpus, exchange = " +
-                                     ("one push kernel over NVLink peer memory (CUDA IPC)" if exchange_kind == "peer"
-                                      else "NCCL all-to-all of 16-byte records")) if world > 1 else "single GPU"},
+            "config": dict(make_config(args.workload, world, exchange_kind),
+                           **({"frames_per_gpu": frames_per_gpu} if args.frames else {})),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks.summary(), "map": {"voxels": n_vox, "occupied": n_occ},
         }
-        if mesh is not None:
-            line["mesh_mask"] = mesh
+        for k, v in (("exchange_check", exchange_check), ("mesh_mask", mesh), ("detector", detector), ("config1", config1),
+                     ("config5", config5)):
+            if v is not None:
+                line[k] = v
         print(json.dumps(line), flush=True)
 
     for e in ev:
@@ -437,7 +486,39 @@ def run_e2e(ctx, pcs, vmap, params, d_in, poses, n_frames, w, h, args, dist, tor
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     s1 = ctx.stats()
-    out = {"value": world * n_pts / (ms / steps * 1e-3), "unit": "points/s",
+    # second, clearly separate figure: the mask only comes back (1 B / point D2H instead of 33).  With
+    # world_frame_output = 0 the annotated cloud differs from the input only in colour / data[3] / padding, which a host
+    # that still owns the input can fill in from the mask (the fused mode of the PointCloudAnnotator adapter).
+    def one_mask_only():
+        vmap.clear()
+        ctx.annotate_frames(h_in, n_frames, w, h, poses, params, vmap, want_annotated=False, mask_out=h_mask)
+        if exch is not None:
+            exch.exchange()
+            ctx.sync()
+
+    one_mask_only()
+    if dist is not None:
+        dist.barrier()
+    m0 = ctx.stats()
+    tm = time.perf_counter()
+    for _ in range(steps):
+        one_mask_only()
+    ctx.sync()
+    ms_mask = (time.perf_counter() - tm) * 1e3
+    if dist is not None:
+        t = torch.tensor([ms_mask], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_mask = float(t.item())
+    m1 = ctx.stats()
+    mask_only = {"value": world * n_pts / (ms_mask / steps * 1e-3), "unit": "points/s", "ms_per_step": ms_mask / steps,
+                 "h2d_bytes_per_step": (m1["bytes_h2d"] - m0["bytes_h2d"]) // steps,
+                 "d2h_bytes_per_step": (m1["bytes_d2h"] - m0["bytes_d2h"]) // steps,
+                 "note": "NOT the headline: mask back only, annotated cloud not copied back"}
+    finite_points = None
+    if dist is not None:  # input of exchange_check: every finite point must be counted exactly once by the exchanged map
+        finite_points = int((np.isfinite(h_in["x"]) & np.isfinite(h_in["y"]) & np.isfinite(h_in["z"])).sum())
+    out = {"value": world * n_pts / (ms / steps * 1e-3), "unit": "points/s", "mask_only": mask_only,
+           "finite_points": finite_points,
            "h2d_bytes_per_step": (s1["bytes_h2d"] - s0["bytes_h2d"]) // steps,
            "d2h_bytes_per_step": (s1["bytes_d2h"] - s0["bytes_d2h"]) // steps, "ms_per_step": ms / steps, "steps": steps,
            "api": "pcs_annotate_frames (host pointers, pinned)", "frames_per_step": n_frames,
@@ -447,6 +528,284 @@ def run_e2e(ctx, pcs, vmap, params, d_in, poses, n_frames, w, h, args, dist, tor
     pin_in.free()
     pin_ann.free()
     pin_mask.free()
+    return out
+
+
+def mix64_np(x: np.ndarray) -> np.ndarray:
+    """pcs_mix64 on an array (owner hash of the multi-GPU exchange)."""
+    x = x.astype(np.uint64).copy()
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(33)
+        x *= np.uint64(0xFF51AFD7ED558CCD)
+        x ^= x >> np.uint64(33)
+        x *= np.uint64(0xC4CEB9FE1A85EC53)
+        x ^= x >> np.uint64(33)
+    return x
+
+
+def map_digest(keys, c0, c1) -> dict:
+    return {"voxels": int(keys.size), "count0_sum": int(c0.sum(dtype=np.uint64)), "count1_sum": int(c1.sum(dtype=np.uint64)),
+            "key_xor": int(np.bitwise_xor.reduce(keys)) if keys.size else 0}
+
+
+def run_exchange_check(ctx, pcs, dist, torch, rank, world, exch, exchange_kind, vmap, params, d_in, d_pose, frames_per_gpu, w,
+                       h, res, cap, finite_points_all_ranks):
+    """Parity self-check of the exchanged map (the multi-GPU parity test cannot run on a 1-GPU test box, this can run in
+    every scaling run).  The owned slices left by the last exchange are exported and gathered; rank 0 integrates the WHOLE
+    scan (the frames of all ranks, regenerated shard by shard) into one map on its own GPU -- the reference semantics: one
+    octree from the concatenation of all frames, octomap_mesh_masking.cpp:105-116 -- and compares voxel by voxel.  A second
+    pass repeats the exchange in the other form (NCCL records vs peer push) and compares the owned slices with the first."""
+    from point_cloud_segmentation_b200.distributed import MapExchange, PeerMapExchange
+
+    def one_exchange(e):
+        vmap.clear()
+        ctx.annotate_frames_dev(d_in, frames_per_gpu, w, h, d_pose, params, vmap, None, None)
+        e.exchange()
+        ctx.sync()
+        owned = e.owned_map if hasattr(e, "owned_map") else e._owned_map
+        return owned.export()
+
+    keys, c0, c1, _ = one_exchange(exch)
+    owner_ok = bool((mix64_np(keys) % np.uint64(world) == np.uint64(rank)).all()) if keys.size else True
+    other_kind = "nccl" if exchange_kind == "peer" else "peer"
+    other_equal = None
+    try:
+        other = (MapExchange if other_kind == "nccl" else PeerMapExchange)(ctx, vmap, dist, torch, cap)
+        k2, a0, a1, _ = one_exchange(other)
+        other_equal = bool(np.array_equal(k2, keys) and np.array_equal(a0, c0) and np.array_equal(a1, c1))
+    except Exception as e:  # e.g. CUDA IPC unavailable: report it, the primary check still stands
+        other_equal = f"unavailable: {e}"
+    gathered = [None] * world
+    dist.all_gather_object(gathered, {"rank": rank, "keys": keys, "c0": c0, "c1": c1, "owner_ok": owner_ok,
+                                      "other_equal": other_equal})
+    out = None
+    if rank == 0:
+        gathered.sort(key=lambda g: g["rank"])
+        all_keys = np.concatenate([g["keys"] for g in gathered])
+        all_c0 = np.concatenate([g["c0"] for g in gathered])
+        all_c1 = np.concatenate([g["c1"] for g in gathered])
+        # one GPU, the whole scan: the shards of all ranks regenerated into rank 0's input buffer one after the other
+        ref = ctx.create_map(res, min(cap * world, 1 << 26))
+        for r in range(world):
+            poses = np.stack([synth_pose(r * frames_per_gpu + f) for f in range(frames_per_gpu)])
+            ctx.h2d(d_pose, poses)
+            ctx.synth_frames_dev(SEED, r * frames_per_gpu, frames_per_gpu, w, h, d_pose, d_in)
+            ctx.annotate_frames_dev(d_in, frames_per_gpu, w, h, d_pose, params, ref, None, None)
+        rk, r0, r1, _ = ref.export()
+        ref.destroy()
+        order = np.argsort(all_keys, kind="stable")
+        rorder = np.argsort(rk, kind="stable")
+        same = bool(all_keys.size == rk.size and np.array_equal(all_keys[order], rk[rorder]) and
+                    np.array_equal(all_c0[order], r0[rorder]) and np.array_equal(all_c1[order], r1[rorder]))
+        exch_d, ref_d = map_digest(all_keys, all_c0, all_c1), map_digest(rk, r0, r1)
+        owners_ok = all(g["owner_ok"] for g in gathered)
+        others = [g["other_equal"] for g in gathered]
+        finite_ok = None
+        if finite_points_all_ranks is not None:
+            finite_ok = bool(exch_d["count0_sum"] + exch_d["count1_sum"] == finite_points_all_ranks)
+        ok = same and owners_ok and exch_d == ref_d and all(o is True for o in others if not isinstance(o, str)) and \
+            (finite_ok is not False)
+        out = {"ok": bool(ok), "exchange": exchange_kind, "exchanged": exch_d, "one_gpu_whole_scan": ref_d,
+               "voxel_by_voxel_equal": same, "owner_ok": owners_ok, "other_form": other_kind,
+               "other_form_equal": others[0] if len(set(map(str, others))) == 1 else others,
+               "finite_points_all_ranks": finite_points_all_ranks, "counts_equal_finite_points": finite_ok,
+               "frames_checked": world * frames_per_gpu}
+    dist.barrier()
+    return out
+
+
+def run_config1(ctx, pcs, peak):
+    """BASELINE configs[0]: one 640x480 frame, HSV annotation + integration at 1 cm through the host-pointer API (what the
+    node does per frame at batch_size = 1), and the mask of a ~10 k-triangle mesh, all three mask types (host API)."""
+    w, h, res = 640, 480, 0.01
+    pose = np.stack([synth_pose(0)])
+    d_pose, d_in = ctx.dev_alloc(pose.nbytes), ctx.dev_alloc(w * h * 32)
+    ctx.h2d(d_pose, pose)
+    ctx.synth_frames_dev(SEED, 0, 1, w, h, d_pose, d_in)
+    pin_in, pin_ann, pin_mask = pcs.capi.PinnedBuffer(w * h * 32), pcs.capi.PinnedBuffer(w * h * 32), pcs.capi.PinnedBuffer(w * h)
+    frame = pin_in.array(pcs.POINT_DTYPE)
+    ann, mask = pin_ann.array(pcs.POINT_DTYPE), pin_mask.array(np.uint8)
+    ctx.d2h(frame, d_in)
+    vmap = ctx.create_map(res, 1 << 18)
+    params = pcs.annotate_params(lower=255, upper=255)
+    reps = 50
+    for _ in range(5):
+        ctx.annotate_frames(frame, 1, w, h, pose, params, vmap, annotated_out=ann, mask_out=mask)
+    l0 = ctx.stats()["kernel_launches"]
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        ctx.annotate_frames(frame, 1, w, h, pose, params, vmap, annotated_out=ann, mask_out=mask)
+    us_host = (time.perf_counter() - t0) / reps * 1e6
+    launches = (ctx.stats()["kernel_launches"] - l0) / reps
+    d_ann, d_mask = ctx.dev_alloc(w * h * 32), ctx.dev_alloc(w * h)
+    evs = [(ctx.event(), ctx.event()) for _ in range(reps)]
+    for a, b in evs:
+        ctx.record(a)
+        ctx.annotate_frames_dev(d_in, 1, w, h, d_pose, params, vmap, d_ann, d_mask)
+        ctx.record(b)
+    ctx.sync()
+    us_dev = float(np.median([ctx.elapsed_ms(a, b) for a, b in evs])) * 1e3
+    for a, b in evs:
+        ctx.event_destroy(a)
+        ctx.event_destroy(b)
+    # ~10 k triangles over the frame's footprint
+    xs, ys = np.linspace(-0.45, 0.45, 101), np.linspace(-0.25, 0.25, 51)
+    gx, gy = np.meshgrid(xs, ys, indexing="xy")
+    verts = np.stack([gx.ravel(), gy.ravel(), 0.02 * np.sin(8.0 * gx.ravel()) * np.cos(6.0 * gy.ravel())], 1)
+    idx = np.arange(101 * 51, dtype=np.int32).reshape(51, 101)
+    a, b, c, d = idx[:-1, :-1].ravel(), idx[:-1, 1:].ravel(), idx[1:, 1:].ravel(), idx[1:, :-1].ravel()
+    tris = np.stack([np.stack([a, b, c], 1), np.stack([a, c, d], 1)], 1).reshape(-1, 3)
+    faces = np.ascontiguousarray(np.concatenate([np.full((tris.shape[0], 1), 3, np.int32), tris], 1).astype(np.int32))
+    mesh = {}
+    for name, mt in (("inside", pcs.RETURN_INSIDE), ("outside", pcs.RETURN_OUTSIDE), ("colorized", pcs.RETURN_COLORIZED)):
+        for _ in range(3):
+            out = ctx.mesh_mask(vmap, verts, faces, mt)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            out = ctx.mesh_mask(vmap, verts, faces, mt)
+        mesh[name] = {"us": (time.perf_counter() - t0) / 20 * 1e6, "triangles_out": int(out[1].shape[0])}
+    n_vox, n_occ = vmap.size()
+    pts = w * h
+    res_out = {"workload": "frame1_640x480_1cm + mesh of 10 000 triangles", "api": "pcs_annotate_frames / pcs_mesh_mask (host pointers)",
+               "frame_us_host_call": us_host, "frame_us_device": us_dev, "kernel_launches_per_frame": launches,
+               "points_per_s_host_call": pts / (us_host * 1e-6), "map": {"voxels": n_vox, "occupied": n_occ},
+               "mesh_triangles": int(faces.shape[0]), "mesh_mask": mesh,
+               "roofline": {"bound": "hbm", "achieved": BYTES_PER_POINT * pts / (us_dev * 1e-6) / 1e9, "peak": peak, "unit": "GB/s",
+                            "frac": BYTES_PER_POINT * pts / (us_dev * 1e-6) / 1e9 / peak, "kernel": "annotate_kernel<map,ann,mask>",
+                            "kernel_ms": us_dev * 1e-3, "note": "one 20 MB frame: launch-latency bound, not bandwidth bound"}}
+    vmap.destroy()
+    for p in (d_pose, d_in, d_ann, d_mask):
+        ctx.dev_free(p)
+    for b in (pin_in, pin_ann, pin_mask):
+        b.free()
+    return res_out
+
+
+def run_config5(ctx, pcs, dist, torch, rank, world, peak, steps, want_exchange):
+    """BASELINE configs[4]: 3840x2160 frames at 2 mm voxels (HBM / atomic stress), 16 frames per GPU, with a voxel table of
+    2^24 slots (268 MB: larger than L2), at every N.  Same step as the headline: clear, fused kernel, exchange."""
+    n_frames, w, h, res, cap = 16, 3840, 2160, 0.002, 1 << 23
+    n_pts = n_frames * w * h
+    first = rank * n_frames
+    poses = np.stack([synth_pose(first + f) for f in range(n_frames)])
+    d_pose, d_in, d_ann, d_mask = ctx.dev_alloc(poses.nbytes), ctx.dev_alloc(n_pts * 32), ctx.dev_alloc(n_pts * 32), ctx.dev_alloc(n_pts)
+    ctx.h2d(d_pose, poses)
+    ctx.synth_frames_dev(SEED, first, n_frames, w, h, d_pose, d_in)
+    vmap = ctx.create_map(res, cap)
+    params = pcs.annotate_params(lower=255, upper=255)
+    exch = None
+    if world > 1 and want_exchange:
+        from point_cloud_segmentation_b200.distributed import PeerMapExchange
+
+        try:
+            exch = PeerMapExchange(ctx, vmap, dist, torch, cap)
+        except Exception:
+            exch = None
+        ok = torch.tensor([1 if exch is not None else 0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 0:
+            exch = None
+    k_evs = [(ctx.event(), ctx.event()) for _ in range(steps)]
+
+    def step(pair=None):
+        vmap.clear()
+        if pair:
+            ctx.record(pair[0])
+        ctx.annotate_frames_dev(d_in, n_frames, w, h, d_pose, params, vmap, d_ann, d_mask)
+        if pair:
+            ctx.record(pair[1])
+        if exch is not None:
+            exch.exchange()
+
+    for _ in range(3):
+        step()
+    ctx.sync()
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = ctx.event(), ctx.event()
+    ctx.record(e0)
+    for i in range(steps):
+        step(k_evs[i])
+    ctx.record(e1)
+    ctx.sync()
+    ms = ctx.elapsed_ms(e0, e1) / steps
+    k_ms = float(np.mean([ctx.elapsed_ms(a, b) for a, b in k_evs]))
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    n_vox, n_occ = vmap.size()
+    achieved = BYTES_PER_POINT * n_pts / (k_ms * 1e-3) / 1e9
+    out = {"workload": "scan16_3840x2160_2mm", "frames_per_gpu": n_frames, "n_gpus": world, "value": world * n_pts / (ms * 1e-3),
+           "unit": "points/s", "ms_per_step": ms, "steps": steps, "voxel_table_bytes": 2 * cap * 16,
+           "map_local": {"voxels": n_vox, "occupied": n_occ}, "exchange": ("peer" if exch is not None else None),
+           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                        "kernel": "annotate_kernel<map,ann,mask>", "kernel_ms": k_ms,
+                        "algorithmic_bytes_per_launch": BYTES_PER_POINT * n_pts}}
+    for a, b in k_evs + [(e0, e1)]:
+        ctx.event_destroy(a)
+        ctx.event_destroy(b)
+    if exch is not None:
+        exch.close()
+    vmap.destroy()
+    for p in (d_pose, d_in, d_ann, d_mask):
+        ctx.dev_free(p)
+    return out
+
+
+def run_detector(ctx, pcs, vmap, params, d_in, d_pose, d_ann, d_mask, frames_per_gpu, w, h, peak, plain_kernel_ms):
+    """The opening path: fused annotate+integrate with morph_open = 1 on the headline scan (annotate_open_kernel) next to
+    the un-opened kernel, and the stage-1 image kernels on a stack of BGR images (4 B / pixel)."""
+    import ctypes as C
+
+    n_pts = frames_per_gpu * w * h
+    p_open = pcs.annotate_params(pcs.hsv_params(morph_open=1), lower=255, upper=255)
+    for _ in range(2):
+        vmap.clear()
+        ctx.annotate_frames_dev(d_in, frames_per_gpu, w, h, d_pose, p_open, vmap, d_ann, d_mask)
+    evs = [(ctx.event(), ctx.event()) for _ in range(5)]
+    for a, b in evs:
+        vmap.clear()
+        ctx.record(a)
+        ctx.annotate_frames_dev(d_in, frames_per_gpu, w, h, d_pose, p_open, vmap, d_ann, d_mask)
+        ctx.record(b)
+    ctx.sync()
+    ms_open = float(np.mean([ctx.elapsed_ms(a, b) for a, b in evs]))
+    for a, b in evs:
+        ctx.event_destroy(a)
+        ctx.event_destroy(b)
+    achieved = BYTES_PER_POINT * n_pts / (ms_open * 1e-3) / 1e9
+    out = {"fused_open": {"ms": ms_open, "points_per_s": n_pts / (ms_open * 1e-3), "ratio_to_unopened_kernel": ms_open / plain_kernel_ms,
+                          "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                                       "kernel": "annotate_open_kernel<map,ann,mask>", "kernel_ms": ms_open}}}
+    # image API: 64 stacked 1280x720 BGR frames (236 MB in, 59 MB out: larger than L2)
+    iw, ih, n = 1280, 720, 64
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, (n * ih, iw, 3), dtype=np.uint8)
+    d_img, d_out = ctx.dev_alloc(img.nbytes), ctx.dev_alloc(n * ih * iw)
+    ctx.h2d(d_img, img)
+    for name, morph in (("image_threshold", 0), ("image_open", 1)):
+        p = pcs.hsv_params(morph_open=morph)
+        call = lambda: pcs.capi._check(ctx.lib.pcs_hsv_mask_dev(ctx.h, C.c_void_p(d_img), iw, n * ih, iw * 3, C.byref(p),
+                                                                C.c_void_p(d_out), iw))
+        for _ in range(3):
+            call()
+        e0, e1 = ctx.event(), ctx.event()
+        ctx.record(e0)
+        for _ in range(10):
+            call()
+        ctx.record(e1)
+        ms = ctx.elapsed_ms(e0, e1) / 10
+        px = n * ih * iw
+        out[name] = {"ms": ms, "pixels_per_s": px / (ms * 1e-3),
+                     "roofline": {"bound": "hbm", "achieved": 4 * px / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                                  "frac": 4 * px / (ms * 1e-3) / 1e9 / peak,
+                                  "kernel": "hsv_open_kernel" if morph else "hsv_mask_flat_kernel", "kernel_ms": ms}}
+        ctx.event_destroy(e0)
+        ctx.event_destroy(e1)
+    ctx.dev_free(d_img)
+    ctx.dev_free(d_out)
     return out
 
 
@@ -517,12 +876,12 @@ def run_mesh(ctx, pcs, vmap, n_frames, peak, reps=10, e2e=True):
         case = {"triangles": nt, "inside_fraction": s_in, "kept_outside": kept,
                 "flags": {"ms": ms_flags, "tris_per_s": nt / (ms_flags * 1e-3), "launches": int(launches_flags),
                           "roofline": {"bound": "hbm", "achieved": b_flags / (ms_flags * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                                       "frac": b_flags / (ms_flags * 1e-3) / 1e9 / peak, "kernel": "mesh_mask_kernel",
+                                       "frac": b_flags / (ms_flags * 1e-3) / 1e9 / peak, "kernel": "mesh_{vertex,tri,undecided,contacts_big}_kernel",
                                        "algorithmic_bytes": b_flags}},
                 "mask": {"ms": ms_mask, "tris_per_s": nt / (ms_mask * 1e-3), "launches": int(launches_mask),
                          "roofline": {"bound": "hbm", "achieved": b_mask / (ms_mask * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                                       "frac": b_mask / (ms_mask * 1e-3) / 1e9 / peak,
-                                      "kernel": "mesh_mask_kernel + compact_{count,scan,scatter}", "algorithmic_bytes": b_mask}}}
+                                      "kernel": "mesh_{vertex,tri,undecided,contacts_big}_kernel + compact_{count,scan,scatter}", "algorithmic_bytes": b_mask}}}
         if e2e:
             t0 = time.perf_counter()
             n_e2e = 3

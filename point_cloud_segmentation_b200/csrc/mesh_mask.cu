@@ -231,12 +231,20 @@ __device__ __forceinline__ unsigned long long vertex_record(const MapView& m, do
   return rec;
 }
 
+// Programmatic dependent launch: the four kernels of a mask call form a chain in one stream.  Each kernel lets its
+// successor be scheduled at once (launch_dependents) and each successor waits (grid_dependency_wait) for its predecessor
+// to have completed and flushed before it touches anything the predecessor wrote, so launch latency and the ramp-up of
+// one kernel overlap the tail of the one before.
+__device__ __forceinline__ void launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 constexpr int kVertPerThread = 2;  // vertices per thread of mesh_vertex_kernel (loads and probes of both in flight)
 
 __global__ void __launch_bounds__(256) mesh_vertex_kernel(MapView m, double res, const double* __restrict__ verts,
                                                          unsigned long long nv, unsigned long long* __restrict__ recs,
                                                          unsigned int* __restrict__ counters)
 {
+  launch_dependents();
   const unsigned long long i0 = (unsigned long long)blockIdx.x * (blockDim.x * kVertPerThread) + threadIdx.x;
   if (i0 == 0)
     counters[0] = counters[1] = 0u;  // to-do and big-triangle counts of this call (first kernel of the call, stream order)
@@ -318,6 +326,7 @@ __global__ void __launch_bounds__(256, 4) mesh_tri_kernel(const double* __restri
                                                          unsigned int* __restrict__ todo_count)
 {
   __shared__ unsigned int s_warp_count[8], s_base;
+  launch_dependents();
   const unsigned int lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   const unsigned long long t0 = (unsigned long long)blockIdx.x * (blockDim.x * kTriPerThread) + threadIdx.x;
   int4 f[kTriPerThread];
@@ -329,6 +338,7 @@ __global__ void __launch_bounds__(256, 4) mesh_tri_kernel(const double* __restri
     if (t < nt)
       f[j] = __ldg(reinterpret_cast<const int4*>(faces4) + t);
   }
+  grid_dependency_wait();  // the faces are the caller's; the records come from mesh_vertex_kernel
   unsigned long long r[kTriPerThread][3];
 #pragma unroll
   for (int j = 0; j < kTriPerThread; j++)
@@ -410,6 +420,8 @@ __global__ void __launch_bounds__(128) mesh_undecided_kernel(const MapView m, do
                                                             unsigned int* __restrict__ big_list,
                                                             unsigned int* __restrict__ big_count)
 {
+  launch_dependents();
+  grid_dependency_wait();
   const unsigned int n_todo = *todo_count;
   const unsigned int lane = threadIdx.x & 31u;
   const unsigned int n_round = (n_todo + 31u) & ~31u;  // whole warps stay converged for the ballots
@@ -464,6 +476,25 @@ __global__ void __launch_bounds__(128) mesh_undecided_kernel(const MapView m, do
         // the vertex voxels are known to be empty when all three records are valid: only the other voxels are probed
         const unsigned long long kmask = 0xffffffffffffull;
         const bool skip = (all & kRecValid) != 0ull;
+        // The probes below depend on each other only through the early exit, but each is a round trip to L2 or HBM:
+        // touch every home slot (and the coordinates the separating-axis test may need) first, so that the walk finds
+        // them in cache.
+        for (int dz = 0; dz < n[2]; dz++)
+          for (int dy = 0; dy < n[1]; dy++)
+            for (int dx = 0; dx < n[0]; dx++)
+            {
+              const unsigned long long key = ((unsigned long long)(lo[2] + dz) << 32) | ((unsigned long long)(lo[1] + dy) << 16) |
+                                             (unsigned long long)(lo[0] + dx);
+              if (skip && (key == (r0 & kmask) || key == (r1 & kmask) || key == (r2 & kmask)))
+                continue;
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(m.slots + (slot_hash(key) & m.mask)));
+            }
+        if (!have_verts)
+        {
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(verts + 3ull * f.y));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(verts + 3ull * f.z));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(verts + 3ull * f.w));
+        }
         for (int dz = 0; dz < n[2] && !flag; dz++)
           for (int dy = 0; dy < n[1] && !flag; dy++)
             for (int dx = 0; dx < n[0] && !flag; dx++)
@@ -531,6 +562,7 @@ __global__ void __launch_bounds__(256) mesh_contacts_big_kernel(MapView m, doubl
                                                                const unsigned int* __restrict__ big_list,
                                                                const unsigned int* __restrict__ big_count)
 {
+  grid_dependency_wait();
   const unsigned int n_big = *big_count;
   if (n_big != 0)
   {
@@ -629,6 +661,23 @@ __global__ void colorize_kernel(const uint8_t* __restrict__ flags, const int* __
     }
 }
 
+template <class... Params, class... Args>
+static cudaError_t launch_chained(void (*kernel)(Params...), unsigned int grid, unsigned int block, cudaStream_t stream,
+                                  bool dependent, Args... args)
+{
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = dependent ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
+}
+
 int mesh_contacts_launch(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev,
                          uint64_t nt, uint8_t* flags_dev)
 {
@@ -647,21 +696,25 @@ int mesh_contacts_launch(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, ui
   unsigned long long* recs = (unsigned long long*)((char*)scr + 2 * list_bytes);
   const unsigned int mx = (unsigned int)ctx->sm_count * 8u;
 
-  mesh_vertex_kernel<<<(unsigned int)((nv + 256 * kVertPerThread - 1) / (256 * kVertPerThread)) + (nv == 0 ? 1u : 0u), 256, 0,
-                       ctx->stream>>>(map->view, map->resolution,
-                                                                                                  verts_dev, nv, recs, counters);
-  mesh_tri_kernel<<<(unsigned int)((nt + 256 * kTriPerThread - 1) / (256 * kTriPerThread)), 256, 0, ctx->stream>>>(
-      verts_dev, nv, faces4_dev, nt, recs, flags_dev, todo, counters);
-  unsigned long long blocks = (nt + 127) / 128;
-  if (blocks > mx)
-    blocks = mx;
-  mesh_undecided_kernel<<<(unsigned int)blocks, 128, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, faces4_dev, recs,
-                                                                      flags_dev, todo, counters, big_list, counters + 1);
-  blocks = (map->n_slots + 255) / 256;
-  if (blocks > (unsigned long long)ctx->sm_count * 4ull)
-    blocks = (unsigned long long)ctx->sm_count * 4ull;
-  mesh_contacts_big_kernel<<<(unsigned int)blocks, 256, 0, ctx->stream>>>(map->view, map->resolution, verts_dev, nv, faces4_dev,
-                                                                        flags_dev, big_list, counters + 1);
+  const unsigned int g_vert = (unsigned int)((nv + 256 * kVertPerThread - 1) / (256 * kVertPerThread)) + (nv == 0 ? 1u : 0u);
+  const unsigned int g_tri = (unsigned int)((nt + 256 * kTriPerThread - 1) / (256 * kTriPerThread));
+  unsigned long long g_und = (nt + 127) / 128;
+  if (g_und > mx)
+    g_und = mx;
+  unsigned long long g_big = (map->n_slots + 255) / 256;
+  if (g_big > (unsigned long long)ctx->sm_count)
+    g_big = (unsigned long long)ctx->sm_count;  // one CTA per SM: with no big triangle (the usual case) it only starts and exits
+  cudaStream_t st = ctx->stream;
+  PCS_CUDA(launch_chained(mesh_vertex_kernel, g_vert, 256, st, false, map->view, map->resolution, verts_dev,
+                          (unsigned long long)nv, recs, counters));
+  PCS_CUDA(launch_chained(mesh_tri_kernel, g_tri, 256, st, true, verts_dev, (unsigned long long)nv, (const int*)faces4_dev,
+                          (unsigned long long)nt, (const unsigned long long*)recs, flags_dev, todo, counters));
+  PCS_CUDA(launch_chained(mesh_undecided_kernel, (unsigned int)g_und, 128, st, true, map->view, map->resolution, verts_dev,
+                          (const int*)faces4_dev, (const unsigned long long*)recs, flags_dev, (const unsigned int*)todo,
+                          (const unsigned int*)counters, big_list, counters + 1));
+  PCS_CUDA(launch_chained(mesh_contacts_big_kernel, (unsigned int)g_big, 256, st, true, map->view, map->resolution, verts_dev,
+                          (unsigned long long)nv, (const int*)faces4_dev, flags_dev, (const unsigned int*)big_list,
+                          (const unsigned int*)(counters + 1)));
   count_launch(ctx, 4);
   return check_launch("mesh_tri_kernel");
 }

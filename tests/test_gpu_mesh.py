@@ -151,6 +151,60 @@ def test_far_vertices_terminate_and_match_the_oracle(ctx, pcs, O):
     vmap.destroy()
 
 
+def test_device_resident_mask_equals_host_call(ctx, pcs, O):
+    """pcs_mesh_mask_dev (mesh and outputs in HBM) against pcs_mesh_mask and the oracle, all three mask types; also vertices
+    exactly on voxel faces, where the per-vertex records widen the key box."""
+    res = 0.01
+    w, h = 320, 240
+    frames = np.concatenate([O.synth_frame(f, w, h) for f in range(2)])
+    poses = np.stack([O.synth_pose(f) for f in range(2)])
+    vmap = ctx.create_map(res, 1 << 18)
+    ctx.annotate_frames(frames, 2, w, h, poses, pcs.annotate_params(lower=255, upper=255), vmap, want_annotated=False,
+                        want_mask=False)
+    keys, c0, c1, _ = vmap.export()
+    # y spacing 0.005 = half a voxel: every second row of vertices lies exactly on a voxel face
+    verts, faces = grid_mesh(90, 200, -0.45, 0.45, -0.5, 0.5, surface)
+    verts[:, 1] = np.round(verts[:, 1] / 0.005) * 0.005
+    verts[::7, 2] = np.round(verts[::7, 2] / res) * res
+    nv, nt = verts.shape[0], faces.shape[0]
+    o_flags = O.mesh_contacts_keys(keys[c1 > 0], res, verts, faces)
+    assert 0.05 < o_flags.mean() < 0.95
+    d_v, d_f, d_fl = ctx.dev_alloc(verts.nbytes), ctx.dev_alloc(faces.nbytes), ctx.dev_alloc(nt)
+    d_ov, d_of, d_rgb, d_n = ctx.dev_alloc(nt * 72), ctx.dev_alloc(nt * 16), ctx.dev_alloc(max(nt * 9, nv * 3)), ctx.dev_alloc(8)
+    ctx.h2d(d_v, verts)
+    ctx.h2d(d_f, faces)
+    for mt in (pcs.RETURN_INSIDE, pcs.RETURN_OUTSIDE, pcs.RETURN_COLORIZED):
+        ctx.mesh_mask_dev(vmap, d_v, nv, d_f, nt, mt, nt, d_ov, d_of, d_rgb, d_fl, d_n)
+        flags, n_out = np.empty(nt, np.uint8), np.zeros(1, np.uint64)
+        ctx.d2h(flags, d_fl)
+        ctx.d2h(n_out, d_n)
+        assert np.array_equal(flags, o_flags)
+        wv, wf, wrgb = O.mask_mesh_emit(verts, faces, o_flags, mt)
+        hv, hf, hrgb, hflags = ctx.mesh_mask(vmap, verts, faces, mt)
+        assert np.array_equal(hflags, o_flags) and hv.tobytes() == wv.tobytes() and np.array_equal(hf, wf) and np.array_equal(hrgb, wrgb)
+        assert int(n_out[0]) == wf.shape[0]
+        if mt == pcs.RETURN_COLORIZED:
+            rgb = np.empty((nv, 3), np.uint8)
+            ctx.d2h(rgb, d_rgb)
+            assert np.array_equal(rgb, wrgb)
+        else:
+            k = wf.shape[0]
+            ov, of, rgb = np.empty((3 * k, 3), np.float64), np.empty((k, 4), np.int32), np.empty((3 * k, 3), np.uint8)
+            if k:
+                ctx.d2h(ov, d_ov)
+                ctx.d2h(of, d_of)
+                ctx.d2h(rgb, d_rgb)
+            assert ov.tobytes() == wv.tobytes() and np.array_equal(of, wf) and np.array_equal(rgb, wrgb)
+    # count-only form
+    ctx.mesh_mask_dev(vmap, d_v, nv, d_f, nt, pcs.RETURN_INSIDE, 0, None, None, None, d_fl, d_n)
+    n_out = np.zeros(1, np.uint64)
+    ctx.d2h(n_out, d_n)
+    assert int(n_out[0]) == int(o_flags.sum())
+    for p in (d_v, d_f, d_fl, d_ov, d_of, d_rgb, d_n):
+        ctx.dev_free(p)
+    vmap.destroy()
+
+
 def test_empty_mesh_and_bad_mask_type(ctx, pcs):
     vmap = ctx.create_map(0.1, 64)
     ov, of, rgb, flags = ctx.mesh_mask(vmap, np.zeros((0, 3)), np.zeros((0, 4), np.int32), pcs.RETURN_OUTSIDE)
