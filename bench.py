@@ -187,6 +187,105 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+class Exchanger:
+    """The map exchange of a step, in one of three forms.
+
+    peer, pipelined (default for N > 1): two local maps alternate; while the fused kernel fills one on the main stream, the
+        other is pushed to its owners on a side stream through a second context (clear of the recycled owned table, push
+        kernel that also empties the local map, flag barrier), ordered by events.  The exchange of scan k overlaps the
+        kernel of scan k + 1; the timed region ends only when the last exchange has completed.
+    peer, in line (--no-pipeline): the same three phases on the main stream after every kernel (phase times with --trace).
+    nccl: pack by owner, all-to-all of 16-byte records, merge (MapExchange), in line."""
+
+    def __init__(self, pcs, ctx, vmap, dist, torch, cap, res, args, local_rank, rank):
+        from point_cloud_segmentation_b200.distributed import MapExchange, PeerMapExchange
+
+        self.ctx, self.torch, self.dist, self.vmap = ctx, torch, dist, vmap
+        self.kind, self.pipelined, self.side, self.ctx_x = args.exchange, False, None, None
+        self.exch, self.k = None, 0
+        self.local_empty = False
+        if self.kind == "peer":
+            try:
+                if not args.no_pipeline:
+                    self.side = torch.cuda.Stream()
+                    self.ctx_x = pcs.Context(local_rank, self.side.cuda_stream)
+                    with torch.cuda.stream(self.side):
+                        self.exch = PeerMapExchange(self.ctx_x, vmap, dist, torch, cap, barrier=args.barrier, clear_local=True)
+                    self.pipelined = True
+                else:
+                    self.exch = PeerMapExchange(ctx, vmap, dist, torch, cap, barrier=args.barrier, clear_local=True)
+            except Exception as e:  # CUDA IPC unavailable on this box: the NCCL-record form gives the same result
+                print(f"[rank {rank}] peer-memory exchange unavailable ({e}); using NCCL records", file=sys.stderr)
+                self.kind, self.pipelined = "nccl", False
+            ok = torch.tensor([1 if self.kind == "peer" else 0], device="cuda")
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                self.kind, self.pipelined = "nccl", False
+        if self.kind == "nccl":
+            self.exch = MapExchange(ctx, vmap, dist, torch, cap)
+        self.locals = [vmap]
+        if self.pipelined:
+            self.locals.append(ctx.create_map(res, cap))
+            self.filled = [ctx.event(), ctx.event()]
+            self.pushed = [ctx.event(), ctx.event()]
+
+    @property
+    def barrier_kind(self):
+        return getattr(self.exch, "barrier_kind", None)
+
+    def owned_map(self):
+        return self.exch.owned_map if hasattr(self.exch, "owned_map") else self.exch._owned_map
+
+    def next_local(self):
+        """The (empty) local map the coming scan integrates into."""
+        if self.pipelined:
+            i = self.k % 2
+            self.ctx.wait_event(self.pushed[i])  # its previous exchange has read and emptied it
+            return self.locals[i]
+        if not self.local_empty:
+            self.vmap.clear()
+        return self.vmap
+
+    def submit(self, mark=None, debug=""):
+        """Hands the local map just filled to the exchange."""
+        if self.pipelined:
+            i = self.k % 2
+            self.ctx.record(self.filled[i])
+            self.ctx_x.wait_event(self.filled[i])
+            with self.torch.cuda.stream(self.side):
+                self.exch.exchange(local=self.locals[i])
+            self.ctx_x.record(self.pushed[i])
+            self.k += 1
+            return
+        if debug == "barriers-only":
+            self.exch._barrier()
+        elif debug != "setup-only":
+            if mark is not None and self.kind == "peer":
+                self.exch.exchange(mark)
+            else:
+                self.exch.exchange()
+            self.local_empty = self.kind == "peer"
+
+    def drain(self):
+        """Main stream waits for every submitted exchange."""
+        if self.pipelined:
+            for e in self.pushed:
+                self.ctx.wait_event(e)
+
+    def run_sync(self, local=None):
+        """One exchange of `local` (default: the first local map), complete on return."""
+        self.ctx.sync()
+        if self.pipelined:
+            self.ctx_x.sync()
+            with self.torch.cuda.stream(self.side):
+                self.exch.exchange(local=local or self.vmap)
+            self.ctx_x.sync()
+        else:
+            self.exch.exchange()
+            self.ctx.sync()
+            self.local_empty = self.kind == "peer"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -199,6 +298,11 @@ def main():
     ap.add_argument("--cpu-frames", type=int, default=200, help="frames of the cpu_baseline sample")
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="multi-GPU map exchange: one kernel over NVLink peer memory, or NCCL all-to-all of records")
+    ap.add_argument("--barrier", default="kernel", choices=["kernel", "flags", "allreduce"],
+                    help="barrier of the peer exchange: epoch words in peer memory signalled and awaited by one small kernel, "
+                         "or by stream memory operations, or a 4-byte NCCL all-reduce")
+    ap.add_argument("--no-pipeline", action="store_true",
+                    help="peer exchange in line on the main stream instead of overlapped with the next scan's kernel")
     ap.add_argument("--exchange-debug", default="", choices=["", "setup-only", "barriers-only"], help=argparse.SUPPRESS)
     ap.add_argument("--trace", default="", help=argparse.SUPPRESS)  # write per-rank per-step kernel start/end times here
     ap.add_argument("--no-e2e", action="store_true")
@@ -256,36 +360,36 @@ def main():
     exch = None
     exchange_kind = None
     if world > 1:
-        from point_cloud_segmentation_b200.distributed import MapExchange, PeerMapExchange
-
-        exchange_kind = args.exchange
-        if exchange_kind == "peer":
-            try:
-                exch = PeerMapExchange(ctx, vmap, dist, torch, cap)
-            except Exception as e:  # CUDA IPC unavailable on this box: the NCCL-record form gives the same result
-                print(f"[rank {rank}] peer-memory exchange unavailable ({e}); using NCCL records", file=sys.stderr)
-                exchange_kind = "nccl"
-            ok = torch.tensor([1 if exchange_kind == "peer" else 0], device="cuda")
-            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-            if int(ok.item()) == 0:
-                exchange_kind = "nccl"
-        if exchange_kind == "nccl":
-            exch = MapExchange(ctx, vmap, dist, torch, cap)
+        exch = Exchanger(pcs, ctx, vmap, dist, torch, cap, res, args, local_rank, rank)
+        exchange_kind = exch.kind
 
     ev = [ctx.event() for _ in range(4)]
 
+    phase_events = []  # --trace: per step, (name, event) after every phase of the step
+
     def step(timed_kernel=None):
-        vmap.clear()
+        marks = None
+        if args.trace and timed_kernel is not None and not (exch is not None and exch.pipelined):
+            marks = []
+            phase_events.append(marks)
+
+            def mark(name):
+                e = ctx.event()
+                ctx.record(e)
+                marks.append((name, e))
+            mark("start")
+        if exch is None:
+            vmap.clear()
+            m = vmap
+        else:
+            m = exch.next_local()
         if timed_kernel is not None:
             ctx.record(timed_kernel[0])
-        ctx.annotate_frames_dev(d_in, frames_per_gpu, w, h, d_pose, params, vmap, d_ann, d_mask)
+        ctx.annotate_frames_dev(d_in, frames_per_gpu, w, h, d_pose, params, m, d_ann, d_mask)
         if timed_kernel is not None:
             ctx.record(timed_kernel[1])
         if exch is not None:
-            if args.exchange_debug == "barriers-only":
-                exch._barrier()
-            elif args.exchange_debug != "setup-only":
-                exch.exchange()
+            exch.submit(mark if marks is not None else None, args.exchange_debug)
 
     def barrier():
         ctx.sync()
@@ -311,6 +415,8 @@ def main():
         for i in range(args.steps):
             host_ts.append(time.perf_counter() - host_t0)
             step(kernel_ms[i])
+        if exch is not None:
+            exch.drain()  # the timed region ends when the last exchange has completed
         ctx.record(ev[1])
         host_ts.append(time.perf_counter() - host_t0)
         barrier()
@@ -321,6 +427,21 @@ def main():
         tr = {"rank": rank, "kernel_start_ms": [ctx.elapsed_ms(ev[0], a) for a, _ in kernel_ms],
               "kernel_end_ms": [ctx.elapsed_ms(ev[0], b) for _, b in kernel_ms], "total_ms": total_ms,
               "host_enqueue_ms": [1e3 * t for t in host_ts]}
+        if phase_events:
+            # microseconds per phase, median over the steps: clear_local = start -> kernel start, then the exchange phases
+            names = [n for n, _ in phase_events[0]]
+            per = {}
+            for si, marks in enumerate(phase_events):
+                t_prev, prev_name = ctx.elapsed_ms(ev[0], marks[0][1]), "start"
+                ks, ke = tr["kernel_start_ms"][si], tr["kernel_end_ms"][si]
+                per.setdefault("clear_local", []).append((ks - t_prev) * 1e3)
+                per.setdefault("kernel", []).append((ke - ks) * 1e3)
+                t_prev = ke
+                for n, e in marks[1:]:
+                    t = ctx.elapsed_ms(ev[0], e)
+                    per.setdefault(n, []).append((t - t_prev) * 1e3)
+                    t_prev = t
+            tr["phase_us_median"] = {k: float(np.median(v)) for k, v in per.items()}
         with open(f"{args.trace}.rank{rank}.json", "w") as f:
             json.dump(tr, f)
     for a, b in kernel_ms:
@@ -335,7 +456,8 @@ def main():
     value = world * n_pts / (ms_per_step * 1e-3)
 
     # ---- checks on the result of the last step (cheap, outside the timed region) ----------------------------
-    n_vox, n_occ = vmap.size()
+    # (N > 1 with the fused clear: the local map is empty by now, the owned slice of the exchanged map is what is left)
+    n_vox, n_occ = (exch.owned_map() if exch is not None else vmap).size()
 
     # ---- roofline of the dominant kernel (annotate_kernel), live CUDA-event duration ---------------------------
     peak, peak_src = peak_hbm_gbs()
@@ -406,8 +528,13 @@ def main():
             "config": dict(make_config(args.workload, world, exchange_kind),
                            **({"frames_per_gpu": frames_per_gpu} if args.frames else {})),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks.summary(), "map": {"voxels": n_vox, "occupied": n_occ},
+            "clocks": clocks.summary(),
+            "map": {"voxels": n_vox, "occupied": n_occ, "which": "owned slice of the exchanged map" if world > 1 else "whole map"},
         }
+        if exch is not None and exch.kind == "peer":
+            line["config"]["exchange_barrier"] = exch.barrier_kind
+            line["config"]["exchange_overlap"] = ("exchange of scan k on a side stream while the kernel of scan k+1 runs "
+                                                  "(two local maps)") if exch.pipelined else "in line after every kernel"
         for k, v in (("exchange_check", exchange_check), ("mesh_mask", mesh), ("detector", detector), ("config1", config1),
                      ("config5", config5)):
             if v is not None:
@@ -464,8 +591,7 @@ def run_e2e(ctx, pcs, vmap, params, d_in, poses, n_frames, w, h, args, dist, tor
         vmap.clear()
         ctx.annotate_frames(h_in, n_frames, w, h, poses, params, vmap, annotated_out=h_ann, mask_out=h_mask)
         if exch is not None:
-            exch.exchange()
-            ctx.sync()
+            exch.run_sync(vmap)
 
     one()  # warm-up (allocates the staging buffers)
     if dist is not None:
@@ -493,8 +619,7 @@ def run_e2e(ctx, pcs, vmap, params, d_in, poses, n_frames, w, h, args, dist, tor
         vmap.clear()
         ctx.annotate_frames(h_in, n_frames, w, h, poses, params, vmap, want_annotated=False, mask_out=h_mask)
         if exch is not None:
-            exch.exchange()
-            ctx.sync()
+            exch.run_sync(vmap)
 
     one_mask_only()
     if dist is not None:
@@ -560,6 +685,10 @@ def run_exchange_check(ctx, pcs, dist, torch, rank, world, exch, exchange_kind, 
     def one_exchange(e):
         vmap.clear()
         ctx.annotate_frames_dev(d_in, frames_per_gpu, w, h, d_pose, params, vmap, None, None)
+        if isinstance(e, Exchanger):
+            e.run_sync(vmap)
+            return e.owned_map().export()
+        ctx.sync()
         e.exchange()
         ctx.sync()
         owned = e.owned_map if hasattr(e, "owned_map") else e._owned_map

@@ -120,6 +120,9 @@ PCS_API int pcs_memcpy_d2h(pcs_ctx* ctx, void* dst_host, const void* src_dev, si
 PCS_API int pcs_memset_dev(pcs_ctx* ctx, void* dst_dev, int value, size_t bytes);
 PCS_API int pcs_event_create(pcs_ctx* ctx, void** event);
 PCS_API int pcs_event_record(pcs_ctx* ctx, void* event);
+/* makes the context's stream wait for `event` (recorded by another context of the same process): lets a second context on
+ * a side stream run the map exchange of one scan while the first integrates the next */
+PCS_API int pcs_stream_wait_event(pcs_ctx* ctx, void* event);
 PCS_API int pcs_event_elapsed_ms(void* start, void* stop, float* ms); /* synchronises on `stop` */
 PCS_API int pcs_event_destroy(void* event);
 
@@ -262,16 +265,32 @@ PCS_API int pcs_map_pack_by_owner_dev(pcs_ctx* ctx, pcs_map* map, int n_owners, 
 PCS_API int pcs_map_merge_records_dev(pcs_ctx* ctx, pcs_map* map, const void* records_dev, uint64_t n);
 PCS_API uint64_t pcs_mix64(uint64_t key48);
 /* Peer-memory form of the exchange (one process per GPU, NVLink / NVSwitch): each rank exports its OWNED map with
- * pcs_map_ipc_export (a 128-byte CUDA IPC handle pair that the host exchanges by any means), opens every peer's
+ * pcs_map_ipc_export (128 bytes holding the CUDA IPC handle, which the host exchanges by any means), opens every peer's
  * handle with pcs_map_ipc_open (same resolution / capacity as at creation; destroy with pcs_map_destroy), and then one
  * kernel, pcs_map_push_to_owners_dev, adds every voxel of the LOCAL map directly into owners[mix64(key48) % n_owners]
- * with system-scope atomics -- no packing, no staging buffers, no collective for the data.  The host must put a
+ * with system-scope atomics -- no packing, no staging buffers, no collective for the data.  clear_local = 1 leaves the
+ * local map empty (as pcs_map_clear would), saving that launch when the next scan follows.  The host must put a
  * barrier across ranks before the push (owned maps cleared everywhere) and after it (all pushes landed).
  * Owner maps may equally be ordinary maps of this process (single-GPU use and tests). */
 PCS_API int pcs_map_ipc_export(pcs_ctx* ctx, pcs_map* map, void* handle128);
 PCS_API int pcs_map_ipc_open(pcs_ctx* ctx, const void* handle128, double resolution, uint64_t capacity_voxels,
                              pcs_map** peer_map);
-PCS_API int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* owners, int n_owners);
+PCS_API int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* owners, int n_owners,
+                                       int clear_local);
+/* The barrier of that exchange without a collective (no counterpart in the reference, which is single-process): every map
+ * carries 16 epoch words that clears do not touch.  After its push, rank r writes the epoch number into word r of every
+ * peer's owned map with pcs_stream_write_u32_dev (cuStreamWriteValue32: ordered after the push in the context's stream)
+ * and waits with pcs_stream_wait_geq_u32_dev (cuStreamWaitValue32, >=) until the words of all peers in its own map have
+ * reached that epoch.  Nothing spins on an SM and the host does not block.  pcs_map_epoch_flag_dev returns the device
+ * address of word `index` of a local or IPC-opened map. */
+PCS_API int pcs_map_epoch_flag_dev(pcs_map* map, int index, void** flag_dev);
+PCS_API int pcs_stream_write_u32_dev(pcs_ctx* ctx, void* flag_dev, uint32_t value);
+PCS_API int pcs_stream_wait_geq_u32_dev(pcs_ctx* ctx, void* flag_dev, uint32_t value);
+/* The same barrier as ONE 32-thread kernel: lane i stores `epoch` into their_flags[i] (this rank's word in peer i's map,
+ * release at system scope) and then waits until my_flags[i] (peer i's word in this rank's map) has reached it.  One launch
+ * instead of 2 n stream operations.  One process per GPU is assumed (the waiting kernel and the kernels it waits for never
+ * share a device); a peer that does not arrive within ~10 s makes the kernel trap rather than hang. */
+PCS_API int pcs_exchange_barrier_dev(pcs_ctx* ctx, void* const* their_flags, void* const* my_flags, int n, uint32_t epoch);
 
 /* ---- stage 4: mesh mask -------------------------------------------------------------------------------------------- */
 /* Replaces OctomapMeshMask::maskMesh(mask_type) (octomap_mesh_masking.h:131, octomap_mesh_masking.cpp:118-283) against

@@ -68,6 +68,7 @@ SIGNATURES = {
     "pcs_memset_dev": (_i, [_vp, _vp, _i, _sz]),
     "pcs_event_create": (_i, [_vp, _pp]),
     "pcs_event_record": (_i, [_vp, _vp]),
+    "pcs_stream_wait_event": (_i, [_vp, _vp]),
     "pcs_event_elapsed_ms": (_i, [_vp, _vp, C.POINTER(C.c_float)]),
     "pcs_event_destroy": (_i, [_vp]),
     "pcs_hsv_mask": (_i, [_vp, _vp, _i, _i, _sz, C.POINTER(HsvParams), _vp, _sz]),
@@ -97,7 +98,11 @@ SIGNATURES = {
     "pcs_mix64": (_u64, [_u64]),
     "pcs_map_ipc_export": (_i, [_vp, _vp, _vp]),
     "pcs_map_ipc_open": (_i, [_vp, _vp, _dbl, _u64, _pp]),
-    "pcs_map_push_to_owners_dev": (_i, [_vp, _vp, _pp, _i]),
+    "pcs_map_push_to_owners_dev": (_i, [_vp, _vp, _pp, _i, _i]),
+    "pcs_map_epoch_flag_dev": (_i, [_vp, _i, _pp]),
+    "pcs_stream_write_u32_dev": (_i, [_vp, _vp, C.c_uint32]),
+    "pcs_stream_wait_geq_u32_dev": (_i, [_vp, _vp, C.c_uint32]),
+    "pcs_exchange_barrier_dev": (_i, [_vp, _pp, _pp, _i, C.c_uint32]),
     "pcs_mesh_mask": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _i, _u64, _vp, _vp, _vp, _vp, _pu64, _pu64]),
     "pcs_mesh_mask_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _i, _u64, _vp, _vp, _vp, _vp, _vp]),
     "pcs_mesh_contacts_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _vp]),
@@ -290,9 +295,15 @@ class VoxelMap:
         self.h = h
         return self
 
-    def push_to_owners_dev(self, owners: "list[VoxelMap]"):
+    def push_to_owners_dev(self, owners: "list[VoxelMap]", clear_local: bool = False):
         arr = (C.c_void_p * len(owners))(*[o.h for o in owners])
-        _check(self.ctx.lib.pcs_map_push_to_owners_dev(self.ctx.h, self.h, arr, len(owners)))
+        _check(self.ctx.lib.pcs_map_push_to_owners_dev(self.ctx.h, self.h, arr, len(owners), int(clear_local)))
+
+    def epoch_flag_dev(self, index: int) -> int:
+        """Device address of exchange epoch word `index` of this (local or IPC-opened) map."""
+        p = C.c_void_p()
+        _check(self.ctx.lib.pcs_map_epoch_flag_dev(self.h, int(index), C.byref(p)))
+        return int(p.value)
 
     def merge_records_dev(self, records_dev: int, n: int):
         _check(self.ctx.lib.pcs_map_merge_records_dev(self.ctx.h, self.h, _p(records_dev), int(n)))
@@ -348,6 +359,18 @@ class Context:
     def memset(self, dptr: int, value: int, nbytes: int):
         _check(self.lib.pcs_memset_dev(self.h, _p(dptr), int(value), int(nbytes)))
 
+    def stream_write_u32(self, flag_dev: int, value: int):
+        _check(self.lib.pcs_stream_write_u32_dev(self.h, _p(flag_dev), int(value) & 0xFFFFFFFF))
+
+    def stream_wait_geq_u32(self, flag_dev: int, value: int):
+        _check(self.lib.pcs_stream_wait_geq_u32_dev(self.h, _p(flag_dev), int(value) & 0xFFFFFFFF))
+
+    def exchange_barrier(self, their_flags: "list[int]", my_flags: "list[int]", epoch: int):
+        n = len(their_flags)
+        a = (C.c_void_p * max(n, 1))(*their_flags)
+        b = (C.c_void_p * max(n, 1))(*my_flags)
+        _check(self.lib.pcs_exchange_barrier_dev(self.h, a, b, n, int(epoch) & 0xFFFFFFFF))
+
     def event(self) -> int:
         e = C.c_void_p()
         _check(self.lib.pcs_event_create(self.h, C.byref(e)))
@@ -355,6 +378,10 @@ class Context:
 
     def record(self, ev: int):
         _check(self.lib.pcs_event_record(self.h, _p(ev)))
+
+    def wait_event(self, ev: int):
+        """Orders this context's stream after `ev` (an event recorded by any context of this process)."""
+        _check(self.lib.pcs_stream_wait_event(self.h, _p(ev)))
 
     def elapsed_ms(self, start: int, stop: int) -> float:
         ms = C.c_float(0)

@@ -289,7 +289,7 @@ int fill_annotate_args(pcs_map* map, const Point8* clouds, unsigned int n_frames
   if (map)
     a.map = map->view;
   else
-    a.map = MapView{ nullptr, 0, nullptr, nullptr, 0.0 };
+    a.map = MapView{ nullptr, 0, nullptr, nullptr, nullptr, 0.0 };
   return PCS_OK;
 }
 

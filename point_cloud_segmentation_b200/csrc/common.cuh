@@ -55,6 +55,8 @@ struct MapView
   unsigned long long mask;     // n_slots - 1 (power of two)
   unsigned int* n_used;        // distinct voxels
   unsigned int* overflow;      // set when a probe sequence wrapped
+  unsigned int* live;          // live[i] = slot claimed by the i-th distinct voxel (i < *n_used): clear / push / export
+                               // walk the live voxels instead of the whole table
   double inv_res;              // 1 / resolution, computed in double on the host like octomap's resolution_factor
 };
 }  // namespace pcs
@@ -65,7 +67,8 @@ struct pcs_map
   double resolution;
   uint64_t capacity_voxels;
   uint64_t n_slots;
-  unsigned int* d_counters;  // [0] n_used, [1] overflow, [2..] scratch counters
+  void* block;               // one allocation: slots | live list | counters (one CUDA IPC handle exports all three)
+  unsigned int* d_counters;  // [0] n_used, [1] overflow, [2..63] scratch counters, [64..79] exchange epoch flags, [127] clear
   bool is_peer;              // memory belongs to another process (opened through CUDA IPC)
 };
 
@@ -185,7 +188,7 @@ __device__ __forceinline__ void map_add(const MapView& m, unsigned long long key
       k = atomicCAS(&s->key, 0ull, want);
       if (k == 0ull)
       {
-        atomicAdd(m.n_used, 1u);
+        m.live[atomicAdd(m.n_used, 1u)] = (unsigned int)slot;
         k = want;
       }
     }
@@ -267,7 +270,7 @@ __device__ __forceinline__ void map_add_warp_end(const MapView& m, const MapProb
       k = atomicCAS(&s->key, 0ull, pr.want);
       if (k == 0ull)
       {
-        atomicAdd(m.n_used, 1u);
+        m.live[atomicAdd(m.n_used, 1u)] = (unsigned int)slot;
         k = pr.want;
       }
     }

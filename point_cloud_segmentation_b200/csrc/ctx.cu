@@ -287,6 +287,14 @@ int pcs_event_record(pcs_ctx* ctx, void* event)
   return PCS_OK;
 }
 
+int pcs_stream_wait_event(pcs_ctx* ctx, void* event)
+{
+  PCS_TRY(pcs::ctx_bind(ctx));
+  PCS_CHECK_ARG(event != nullptr, "event is NULL");
+  PCS_CUDA(cudaStreamWaitEvent(ctx->stream, (cudaEvent_t)event, 0));
+  return PCS_OK;
+}
+
 int pcs_event_elapsed_ms(void* start, void* stop, float* ms)
 {
   PCS_CHECK_ARG(start && stop && ms, "NULL argument");

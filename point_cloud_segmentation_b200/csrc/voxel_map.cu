@@ -6,6 +6,7 @@
 // hit, clamped at logodds(0.971), early return once clamped) and the pointer tree reduces to a count per key.
 // Export re-creates the octree's view: records in Morton (child-index DFS) order with the float log-odds.
 #include <cub/device/device_radix_sort.cuh>
+#include <cuda.h>
 
 #include <math.h>
 #include <string.h>
@@ -167,6 +168,10 @@ __global__ void owner_scatter_kernel(MapView m, unsigned int n_owners, const uns
   }
 }
 
+constexpr int kCounterWords = 128;
+constexpr int kEpochFlagWord = 64;   // [64, 80): exchange epoch flags, one per peer rank (never reset)
+constexpr int kClearDoneWord = 127;  // CTAs done in map_clear_kernel / map_push_to_owners_kernel (back to 0 when they end)
+
 // ---- peer-memory exchange: every used slot of the local table is added straight into its owner's table ----------------
 // The owner tables may live on other GPUs (CUDA IPC mappings reached over NVLink), so the insert uses system-scope
 // atomics: a 64-bit CAS claims the slot at the owner's L2, a 64-bit add merges the two counters.
@@ -175,7 +180,10 @@ struct OwnerViews
   MapView v[16];
 };
 
-__device__ __forceinline__ void map_add_system(const MapView& m, unsigned long long key48, unsigned long long add)
+// adds `add` to voxel key48 of a (possibly remote) table; returns true if this call claimed a new slot (*slot_out),
+// in which case the caller appends it to the table's live list
+__device__ __forceinline__ bool map_add_system(const MapView& m, unsigned long long key48, unsigned long long add,
+                                               unsigned int* slot_out)
 {
   const unsigned long long want = key48 | kValidBit;
   unsigned long long slot = slot_hash(key48) & m.mask;
@@ -183,33 +191,102 @@ __device__ __forceinline__ void map_add_system(const MapView& m, unsigned long l
   for (unsigned int probe = 0; probe < 65536u; ++probe)
   {
     Slot* s = m.slots + slot;
-    unsigned long long k = atomicCAS_system(&s->key, 0ull, want);  // one round trip: claims or reads the key
-    if (k == 0ull)
-    {
-      atomicAdd_system(m.n_used, 1u);
-      k = want;
-    }
-    if (k == want)
+    const unsigned long long k = atomicCAS_system(&s->key, 0ull, want);  // one round trip: claims or reads the key
+    if (k == 0ull || k == want)
     {
       atomicAdd_system(&s->counts, add);
-      return;
+      *slot_out = (unsigned int)slot;
+      return k == 0ull;
     }
     slot = (slot + 1) & m.mask;
   }
   *m.overflow = 1u;
+  return false;
 }
 
-__global__ void map_push_to_owners_kernel(MapView local, OwnerViews owners, unsigned int n_owners)
+// Walks the live voxels of the local table (not its slots: a table sized for the worst case is mostly empty) and adds
+// each to its owner's table.  New claims are appended to the owner's live list with ONE system-scope atomic per warp and
+// owner (the lanes that claimed a slot in the same table are counted with a ballot): a returning atomic per voxel on one
+// remote address was the dominant cost of the exchange.  With clear_local the kernel also leaves the local table empty
+// (each slot is zeroed once it has been read, the last CTA resets the counters), which saves the separate clear.
+__global__ void __launch_bounds__(256) map_push_to_owners_kernel(MapView local, OwnerViews owners, unsigned int n_owners,
+                                                                int clear_local, unsigned int* __restrict__ local_counters)
 {
-  const unsigned long long n_slots = local.mask + 1;
-  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_slots;
-       i += (unsigned long long)gridDim.x * blockDim.x)
+  const unsigned int n = *local.n_used;
+  const unsigned int lane = threadIdx.x & 31u;
+  const unsigned int n_round = (n + 31u) & ~31u;  // whole warps stay converged for the ballots
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x)
   {
-    const Slot s = local.slots[i];
-    if (!s.key)
-      continue;
-    const unsigned long long k = s.key & ~kValidBit;
-    map_add_system(owners.v[mix64(k) % n_owners], k, s.counts);
+    bool claimed = false;
+    unsigned int owner = 0, new_slot = 0;
+    if (i < n)
+    {
+      const unsigned int ls = local.live[i];
+      const Slot s = local.slots[ls];
+      if (clear_local)
+        reinterpret_cast<uint4*>(local.slots)[ls] = make_uint4(0u, 0u, 0u, 0u);
+      const unsigned long long k = s.key & ~kValidBit;
+      owner = (unsigned int)(mix64(k) % n_owners);
+      claimed = map_add_system(owners.v[owner], k, s.counts, &new_slot);
+    }
+    unsigned int pending = __ballot_sync(0xffffffffu, claimed);
+    while (pending)
+    {
+      const int leader = __ffs(pending) - 1;
+      const unsigned int o = __shfl_sync(0xffffffffu, owner, leader);
+      const unsigned int grp = __ballot_sync(0xffffffffu, claimed && owner == o);
+      unsigned int base = 0;
+      if ((int)lane == leader)
+        base = atomicAdd_system(owners.v[o].n_used, (unsigned int)__popc(grp));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (claimed && owner == o)
+        owners.v[o].live[base + __popc(grp & ((1u << lane) - 1u))] = new_slot;
+      pending &= ~grp;
+    }
+  }
+  if (clear_local)
+  {
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+      __threadfence();
+      if (atomicAdd(&local_counters[kClearDoneWord], 1u) == gridDim.x - 1)
+      {
+        for (int c = 0; c < 64; c++)
+          local_counters[c] = 0u;
+        local_counters[kClearDoneWord] = 0u;
+      }
+    }
+  }
+}
+
+// Clears a table in time proportional to its live voxels: the claimed slots are zeroed through the live list (or the
+// whole table linearly when more than an eighth of it is in use), then the last CTA to finish resets the counters.
+__global__ void __launch_bounds__(256) map_clear_kernel(MapView m, unsigned int* __restrict__ counters)
+{
+  const unsigned int n = *m.n_used;
+  const unsigned long long n_slots = m.mask + 1;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  const unsigned long long first = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((unsigned long long)n > n_slots / 8 || *m.overflow)
+  {
+    uint4* p = reinterpret_cast<uint4*>(m.slots);
+    for (unsigned long long i = first; i < n_slots; i += stride)
+      p[i] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  else
+    for (unsigned long long i = first; i < n; i += stride)
+      reinterpret_cast<uint4*>(m.slots)[m.live[i]] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+  if (threadIdx.x == 0)
+  {
+    __threadfence();
+    if (atomicAdd(&counters[kClearDoneWord], 1u) == gridDim.x - 1)
+    {
+      for (int i = 0; i < 64; i++)
+        counters[i] = 0u;
+      counters[kClearDoneWord] = 0u;
+    }
   }
 }
 
@@ -218,6 +295,24 @@ static unsigned int table_grid(pcs_ctx* ctx, unsigned long long n)
   unsigned long long b = (n + 255) / 256;
   const unsigned long long mx = (unsigned long long)ctx->sm_count * 8ull;
   return (unsigned int)(b < mx ? (b ? b : 1) : mx);
+}
+
+// one allocation per map: slots (16 B each) | live list (4 B per slot) | counters (512 B); peers map it with one IPC handle
+static size_t map_block_bytes(uint64_t n_slots)
+{
+  return (size_t)n_slots * sizeof(Slot) + (size_t)n_slots * sizeof(unsigned int) + kCounterWords * sizeof(unsigned int);
+}
+
+static void map_block_views(pcs_map* m, double resolution)
+{
+  char* base = (char*)m->block;
+  m->view.slots = (Slot*)base;
+  m->view.live = (unsigned int*)(base + (size_t)m->n_slots * sizeof(Slot));
+  m->d_counters = (unsigned int*)(base + (size_t)m->n_slots * (sizeof(Slot) + sizeof(unsigned int)));
+  m->view.mask = m->n_slots - 1;
+  m->view.n_used = m->d_counters;
+  m->view.overflow = m->d_counters + 1;
+  m->view.inv_res = 1.0 / resolution;  // octomap: resolution_factor = 1. / resolution
 }
 
 static int read_counters(pcs_ctx* ctx, pcs_map* map, unsigned int out[2])
@@ -269,22 +364,24 @@ int pcs_map_create(pcs_ctx* ctx, double resolution, uint64_t capacity_voxels, pc
   m->is_peer = false;
   m->d_counters = nullptr;
   m->view.slots = nullptr;
-  cudaError_t e = cudaMalloc(&m->view.slots, n_slots * sizeof(Slot));
-  if (e == cudaSuccess)
-    e = cudaMalloc(&m->d_counters, 64 * sizeof(unsigned int));
+  m->block = nullptr;
+  const size_t bytes = map_block_bytes(n_slots);
+  cudaError_t e = cudaMalloc(&m->block, bytes);
   if (e != cudaSuccess)
   {
-    if (m->view.slots)
-      cudaFree(m->view.slots);
     delete m;
     return cuda_fail(e, "cudaMalloc(voxel map)", __FILE__, __LINE__);
   }
-  m->view.mask = n_slots - 1;
-  m->view.n_used = m->d_counters;
-  m->view.overflow = m->d_counters + 1;
-  m->view.inv_res = 1.0 / resolution;  // octomap: resolution_factor = 1. / resolution
+  map_block_views(m, resolution);
+  e = cudaMemsetAsync(m->block, 0, bytes, ctx->stream);  // the only full memset: clears walk the live list
+  if (e != cudaSuccess)
+  {
+    cudaFree(m->block);
+    delete m;
+    return cuda_fail(e, "cudaMemsetAsync(voxel map)", __FILE__, __LINE__);
+  }
   *out = m;
-  return pcs_map_clear(ctx, m);
+  return PCS_OK;
 }
 
 int pcs_map_destroy(pcs_ctx* ctx, pcs_map* map)
@@ -294,15 +391,9 @@ int pcs_map_destroy(pcs_ctx* ctx, pcs_map* map)
   PCS_TRY(ctx_bind(ctx));
   PCS_CUDA(cudaStreamSynchronize(ctx->stream));
   if (map->is_peer)
-  {
-    cudaIpcCloseMemHandle(map->view.slots);
-    cudaIpcCloseMemHandle(map->d_counters);
-  }
+    cudaIpcCloseMemHandle(map->block);
   else
-  {
-    cudaFree(map->view.slots);
-    cudaFree(map->d_counters);
-  }
+    cudaFree(map->block);
   delete map;
   return PCS_OK;
 }
@@ -311,9 +402,9 @@ int pcs_map_clear(pcs_ctx* ctx, pcs_map* map)
 {
   PCS_TRY(ctx_bind(ctx));
   PCS_CHECK_ARG(map != nullptr, "map is NULL");
-  PCS_CUDA(cudaMemsetAsync(map->view.slots, 0, map->n_slots * sizeof(Slot), ctx->stream));
-  PCS_CUDA(cudaMemsetAsync(map->d_counters, 0, 64 * sizeof(unsigned int), ctx->stream));
-  return PCS_OK;
+  map_clear_kernel<<<(unsigned int)ctx->sm_count * 2u, 256, 0, ctx->stream>>>(map->view, map->d_counters);
+  count_launch(ctx);
+  return check_launch("map_clear_kernel");
 }
 
 int pcs_map_size(pcs_ctx* ctx, pcs_map* map, uint64_t* n_voxels, uint64_t* n_occupied)
@@ -445,8 +536,8 @@ int pcs_map_ipc_export(pcs_ctx* ctx, pcs_map* map, void* handle128)
   PCS_CHECK_ARG(!map->is_peer, "cannot re-export a peer map");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   cudaIpcMemHandle_t h[2];
-  PCS_CUDA(cudaIpcGetMemHandle(&h[0], map->view.slots));
-  PCS_CUDA(cudaIpcGetMemHandle(&h[1], map->d_counters));
+  memset(h, 0, sizeof(h));  // the second half of the 128 bytes is reserved (the map is one allocation)
+  PCS_CUDA(cudaIpcGetMemHandle(&h[0], map->block));
   memcpy(handle128, h, sizeof(h));
   return PCS_OK;
 }
@@ -462,31 +553,141 @@ int pcs_map_ipc_open(pcs_ctx* ctx, const void* handle128, double resolution, uin
     n_slots <<= 1;
   cudaIpcMemHandle_t h[2];
   memcpy(h, handle128, sizeof(h));
-  void *slots = nullptr, *counters = nullptr;
-  PCS_CUDA(cudaIpcOpenMemHandle(&slots, h[0], cudaIpcMemLazyEnablePeerAccess));
-  cudaError_t e = cudaIpcOpenMemHandle(&counters, h[1], cudaIpcMemLazyEnablePeerAccess);
-  if (e != cudaSuccess)
-  {
-    cudaIpcCloseMemHandle(slots);
-    return cuda_fail(e, "cudaIpcOpenMemHandle(counters)", __FILE__, __LINE__);
-  }
+  void* block = nullptr;
+  PCS_CUDA(cudaIpcOpenMemHandle(&block, h[0], cudaIpcMemLazyEnablePeerAccess));
   pcs_map* m = new (std::nothrow) pcs_map();
-  PCS_CHECK_ARG(m != nullptr, "out of host memory");
+  if (!m)
+  {
+    cudaIpcCloseMemHandle(block);
+    set_error("out of host memory");
+    return PCS_ERR_BAD_ARG;
+  }
   m->resolution = resolution;
   m->capacity_voxels = capacity_voxels;
   m->n_slots = n_slots;
   m->is_peer = true;
-  m->d_counters = (unsigned int*)counters;
-  m->view.slots = (Slot*)slots;
-  m->view.mask = n_slots - 1;
-  m->view.n_used = m->d_counters;
-  m->view.overflow = m->d_counters + 1;
-  m->view.inv_res = 1.0 / resolution;
+  m->block = block;
+  map_block_views(m, resolution);
   *out = m;
   return PCS_OK;
 }
 
-int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* owners, int n_owners)
+// ---- stream-ordered flags: the barrier of the peer-memory exchange without a collective and without a spinning kernel ----
+typedef CUresult (*stream_write32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+typedef CUresult (*stream_wait32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+
+static int stream_memops(stream_write32_fn* wr, stream_wait32_fn* wt)
+{
+  static stream_write32_fn s_wr = nullptr;
+  static stream_wait32_fn s_wt = nullptr;
+  if (!s_wr || !s_wt)
+  {
+    cudaDriverEntryPointQueryResult q1, q2;
+    void *p1 = nullptr, *p2 = nullptr;
+    PCS_CUDA(cudaGetDriverEntryPoint("cuStreamWriteValue32", &p1, cudaEnableDefault, &q1));
+    PCS_CUDA(cudaGetDriverEntryPoint("cuStreamWaitValue32", &p2, cudaEnableDefault, &q2));
+    if (q1 != cudaDriverEntryPointSuccess || q2 != cudaDriverEntryPointSuccess || !p1 || !p2)
+    {
+      set_error("the driver does not offer cuStreamWriteValue32 / cuStreamWaitValue32");
+      return PCS_ERR_CUDA;
+    }
+    s_wr = (stream_write32_fn)p1;
+    s_wt = (stream_wait32_fn)p2;
+  }
+  *wr = s_wr;
+  *wt = s_wt;
+  return PCS_OK;
+}
+
+int pcs_map_epoch_flag_dev(pcs_map* map, int index, void** flag_dev)
+{
+  PCS_CHECK_ARG(map && flag_dev, "NULL argument");
+  PCS_CHECK_ARG(index >= 0 && index < 16, "flag index must be in [0, 16)");
+  *flag_dev = map->d_counters + kEpochFlagWord + index;
+  return PCS_OK;
+}
+
+int pcs_stream_write_u32_dev(pcs_ctx* ctx, void* flag_dev, uint32_t value)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(flag_dev != nullptr && ((uintptr_t)flag_dev & 3u) == 0, "flag pointer must be a 4-byte aligned device address");
+  stream_write32_fn wr;
+  stream_wait32_fn wt;
+  PCS_TRY(stream_memops(&wr, &wt));
+  const CUresult r = wr((CUstream)ctx->stream, (CUdeviceptr)(uintptr_t)flag_dev, value, CU_STREAM_WRITE_VALUE_DEFAULT);
+  if (r != CUDA_SUCCESS)
+  {
+    set_error("cuStreamWriteValue32 failed with CUresult %d", (int)r);
+    return PCS_ERR_CUDA;
+  }
+  return PCS_OK;
+}
+
+int pcs_stream_wait_geq_u32_dev(pcs_ctx* ctx, void* flag_dev, uint32_t value)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(flag_dev != nullptr && ((uintptr_t)flag_dev & 3u) == 0, "flag pointer must be a 4-byte aligned device address");
+  stream_write32_fn wr;
+  stream_wait32_fn wt;
+  PCS_TRY(stream_memops(&wr, &wt));
+  const CUresult r = wt((CUstream)ctx->stream, (CUdeviceptr)(uintptr_t)flag_dev, value, CU_STREAM_WAIT_VALUE_GEQ);
+  if (r != CUDA_SUCCESS)
+  {
+    set_error("cuStreamWaitValue32 failed with CUresult %d", (int)r);
+    return PCS_ERR_CUDA;
+  }
+  return PCS_OK;
+}
+
+// One small kernel as the barrier: lane i publishes this rank's epoch in peer i's word (release, system scope) and then
+// waits for peer i's epoch in this rank's own word (acquire).  Every rank runs on its own GPU, so the wait cannot starve
+// the kernel it waits for; a peer that never arrives (crashed process) trips the cycle budget and the kernel traps instead
+// of hanging the device.
+struct BarrierFlags
+{
+  unsigned int* theirs[16];
+  unsigned int* mine[16];
+};
+
+__global__ void exchange_barrier_kernel(BarrierFlags f, int n, unsigned int epoch)
+{
+  const int i = (int)threadIdx.x;
+  if (i >= n)
+    return;
+  __threadfence_system();
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f.theirs[i]), "r"(epoch) : "memory");
+  const long long t0 = clock64();
+  for (;;)
+  {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f.mine[i]) : "memory");
+    if ((int)(v - epoch) >= 0)
+      break;
+    if (clock64() - t0 > 20000000000ll)  // ~10 s: a peer is gone
+      __trap();
+  }
+}
+
+int pcs_exchange_barrier_dev(pcs_ctx* ctx, void* const* their_flags, void* const* my_flags, int n, uint32_t epoch)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(n >= 0 && n <= 16, "n must be in [0, 16]");
+  if (n == 0)
+    return PCS_OK;
+  PCS_CHECK_ARG(their_flags && my_flags, "NULL argument");
+  BarrierFlags f;
+  for (int i = 0; i < 16; i++)
+  {
+    f.theirs[i] = i < n ? (unsigned int*)their_flags[i] : nullptr;
+    f.mine[i] = i < n ? (unsigned int*)my_flags[i] : nullptr;
+    PCS_CHECK_ARG(i >= n || (f.theirs[i] && f.mine[i]), "NULL flag pointer");
+  }
+  exchange_barrier_kernel<<<1, 32, 0, ctx->stream>>>(f, n, epoch);
+  count_launch(ctx);
+  return check_launch("exchange_barrier_kernel");
+}
+
+int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* owners, int n_owners, int clear_local)
 {
   PCS_TRY(ctx_bind(ctx));
   PCS_CHECK_ARG(local && owners, "NULL argument");
@@ -499,7 +700,12 @@ int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* own
     PCS_CHECK_ARG(owners[o]->resolution == local->resolution, "owner map resolution differs");
     ov.v[o] = owners[o]->view;
   }
-  map_push_to_owners_kernel<<<table_grid(ctx, local->n_slots), 256, 0, ctx->stream>>>(local->view, ov, (unsigned int)n_owners);
+  // the grid is sized for the capacity (the live count stays on the device); CTAs beyond the live voxels exit at once
+  unsigned int grid = table_grid(ctx, local->capacity_voxels);
+  if (grid > (unsigned int)ctx->sm_count * 2u)
+    grid = (unsigned int)ctx->sm_count * 2u;
+  map_push_to_owners_kernel<<<grid, 256, 0, ctx->stream>>>(local->view, ov, (unsigned int)n_owners, clear_local ? 1 : 0,
+                                                           local->d_counters);
   count_launch(ctx);
   return check_launch("map_push_to_owners_kernel");
 }

@@ -133,6 +133,16 @@ class MapExchange:
         return int(sz.sum())
 
 
+def _push(ctx, local, owners, clear_local):
+    """pcs_map_push_to_owners_dev on `ctx`'s stream (a map handle is not tied to the context that created it)."""
+    import ctypes as C
+
+    from . import capi
+
+    arr = (C.c_void_p * len(owners))(*[o.h for o in owners])
+    capi._check(ctx.lib.pcs_map_push_to_owners_dev(ctx.h, local.h, arr, len(owners), int(clear_local)))
+
+
 class PeerMapExchange:
     """Owner-partitioned reduction through peer memory: local voxels are pushed into the owners' tables by one kernel.
 
@@ -140,13 +150,21 @@ class PeerMapExchange:
     each rank opens its peers' tables.  exchange() number e: clear the table of the other parity (it held the result of
     exchange e - 1, consumed by now), push kernel into the tables of parity e % 2, one barrier (every push has landed).
     The double buffer is what makes a single barrier enough: a peer can only push into my parity-(e+1) table after it
-    has passed barrier e, which I enter after my clear of that table has been enqueued.  The barrier is a 4-byte NCCL
-    all-reduce on the shared stream, so the host never blocks.  `owned_map` is the table holding the latest result; it
-    stays valid until the next exchange() call."""
+    has passed barrier e, which I signal after my clear of that table has been enqueued.
 
-    def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int):
+    The barrier is made of epoch words in peer memory: after its push rank r writes e into word r of every peer's parity-0
+    table and waits for the words of all peers in its own table.  barrier="kernel" (default) does both in one 32-thread
+    kernel (pcs_exchange_barrier_dev; one process per GPU, so the waiting kernel cannot starve the one it waits for);
+    barrier="flags" uses stream memory operations instead (cuStreamWriteValue32 / cuStreamWaitValue32: nothing runs on an
+    SM, but 2 (N-1) stream operations cost more than the one launch: 38 vs 13 us at 8 GPUs).  No collective and no host
+    synchronisation either way.  barrier="allreduce" is the first form, a 4-byte NCCL all-reduce on the shared stream; it is also
+    the fallback when the driver refuses the stream memory operations on IPC memory.  `owned_map` is the table holding the
+    latest result; it stays valid until the next exchange() call."""
+
+    def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int, barrier: str = "kernel", clear_local: bool = False):
         from . import capi
 
+        self.clear_local = clear_local  # the push kernel leaves the local map empty (saves the caller's clear)
         check_shared_stream(ctx, torch)
         self.ctx, self.local, self.dist, self.torch = ctx, vmap, dist, torch
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
@@ -155,6 +173,7 @@ class PeerMapExchange:
         ctx.sync()
         mine = torch.tensor(list(self._mine[0].ipc_export() + self._mine[1].ipc_export()), dtype=torch.uint8,
                             device=self.device)
+        assert self.world <= 16, "the exchange tracks at most 16 ranks"
         allh = torch.empty(self.world * 256, dtype=torch.uint8, device=self.device)
         dist.all_gather_into_tensor(allh, mine)
         allh = allh.cpu().numpy().tobytes()
@@ -169,6 +188,25 @@ class PeerMapExchange:
         self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._epoch = 0
         self.owned_map = self._mine[0]
+        # flag barrier: my word in every peer's parity-0 table, and the peers' words in mine
+        self.barrier_kind = barrier
+        if barrier in ("flags", "kernel"):
+            try:
+                self._their_flag = [self._owners[0][r].epoch_flag_dev(self.rank) for r in range(self.world) if r != self.rank]
+                self._my_flags = [self._mine[0].epoch_flag_dev(r) for r in range(self.world) if r != self.rank]
+                if barrier == "flags":  # probe: the driver must accept stream memory operations on IPC memory
+                    for f in self._their_flag:
+                        ctx.stream_write_u32(f, 0)
+                    for f in self._my_flags:
+                        ctx.stream_wait_geq_u32(f, 0)
+                    ctx.sync()
+                ok = 1
+            except Exception:
+                ok = 0
+            flag = torch.tensor([ok], device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 0:
+                self.barrier_kind = "allreduce"
         dist.barrier()
 
     @property
@@ -176,13 +214,33 @@ class PeerMapExchange:
         return GpuMapAdapter(self.ctx, self.owned_map)
 
     def _barrier(self):
-        self.dist.all_reduce(self._token)  # stream-ordered, no host synchronisation
+        if self.barrier_kind == "kernel":
+            self.ctx.exchange_barrier(self._their_flag, self._my_flags, self._epoch + 1)
+        elif self.barrier_kind == "flags":
+            e = self._epoch + 1  # epochs count from 1: the words start at 0
+            for f in self._their_flag:
+                self.ctx.stream_write_u32(f, e)
+            for f in self._my_flags:
+                self.ctx.stream_wait_geq_u32(f, e)
+        else:
+            self.dist.all_reduce(self._token)  # stream-ordered, no host synchronisation
 
-    def exchange(self):
+    def exchange(self, mark=None, local=None):
+        """`mark`, if given, is called after each phase (clear, push, barrier) -- bench.py records CUDA events there.
+        `local` overrides the map that is pushed (a pipeline that alternates two local maps, one being filled while the
+        other is exchanged on this exchange's own stream)."""
         b = self._epoch % 2
         self._mine[1 - b].clear()                      # result of the previous exchange: consumed, recycle it
-        self.local.push_to_owners_dev(self._owners[b])
+        if mark:
+            mark("clear_owned")
+        src = self.local if local is None else local
+        # the maps are plain device tables: every call below runs on THIS exchange's context (stream), whoever made them
+        _push(self.ctx, src, self._owners[b], self.clear_local)
+        if mark:
+            mark("push")
         self._barrier()                                # all pushes into parity b have landed everywhere
+        if mark:
+            mark("barrier")
         self.owned_map = self._mine[b]
         self._epoch += 1
 

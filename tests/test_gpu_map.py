@@ -153,4 +153,16 @@ def test_push_to_owners_partitions_the_map(ctx, pcs, O):
             m.destroy()
     with pytest.raises(pcs.PcsError):
         local.push_to_owners_dev([local])
+    # clear_local: the push also leaves the local map empty and ready for the next scan
+    a, b = ctx.create_map(0.01, 1 << 17), ctx.create_map(0.01, 1 << 17)
+    want = local.export()
+    local.push_to_owners_dev([a], clear_local=True)
+    assert local.size() == (0, 0)
+    assert all(np.array_equal(x, y) for x, y in zip(a.export(), want))
+    local.integrate(cloud, None, 0, 120)  # the emptied table takes the same scan again
+    assert all(np.array_equal(x, y) for x, y in zip(local.export(), want))
+    local.push_to_owners_dev([b], clear_local=True)
+    assert all(np.array_equal(x, y) for x, y in zip(b.export(), want))
+    a.destroy()
+    b.destroy()
     local.destroy()
