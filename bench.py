@@ -479,6 +479,8 @@ def main():
     mesh = None
     if sub and not args.no_mesh and world == 1:
         mesh = run_mesh(ctx, pcs, vmap, frames_per_gpu, peak)
+    if sub and not args.no_mesh and world > 1 and exch is not None:
+        mesh = run_mesh_multi(ctx, pcs, dist, torch, rank, world, exch, res, cap, frames_per_gpu, peak)
 
     # ---- the opening path (fused kernel with morph_open, image kernels): rank 0 ---------------------------------
     detector = None
@@ -739,6 +741,81 @@ def run_exchange_check(ctx, pcs, dist, torch, rank, world, exch, exchange_kind, 
                "other_form_equal": others[0] if len(set(map(str, others))) == 1 else others,
                "finite_points_all_ranks": finite_points_all_ranks, "counts_equal_finite_points": finite_ok,
                "frames_checked": world * frames_per_gpu}
+    dist.barrier()
+    return out
+
+
+def run_mesh_multi(ctx, pcs, dist, torch, rank, world, exch, res, cap, frames_per_gpu, peak, reps=10):
+    """The mesh mask at N > 1 (north_star: "the mesh mask runs on the gathered map"): the owned slices are all-gathered
+    into a full map on every rank, the 2 M triangles are split evenly over the ranks, each rank decides its range, the
+    flags are all-gathered (every rank ends with all nt flags) and rank 0 emits the compacted OUTSIDE mesh.  Timed: the
+    sharded flag pass (slice kernels + all-gather of the flags, L2 flushed before), max over ranks; the one-off map
+    all-gather and rank 0's emit are reported beside it."""
+    from point_cloud_segmentation_b200.distributed import GpuMapAdapter, allgather_map, sharded_mesh_flags
+
+    device = torch.device("cuda", ctx.device)
+    full = ctx.create_map(res, min(cap * world, 1 << 25))
+    owned = GpuMapAdapter(ctx, exch.owned_map())
+    ctx.sync()
+    dist.barrier()
+    t0 = time.perf_counter()
+    n_total, _, _ = allgather_map(owned, GpuMapAdapter(ctx, full), dist, torch, device)
+    ctx.sync()
+    gather_ms = (time.perf_counter() - t0) * 1e3
+    n_frames_total = world * frames_per_gpu
+    verts, faces = heightfield(n_frames_total, 0.5)  # the s~0.5 case over the footprint of all ranks' frames
+    nv, nt = verts.shape[0], faces.shape[0]
+    d_v, d_f = ctx.dev_alloc(verts.nbytes), ctx.dev_alloc(faces.nbytes)
+    ctx.h2d(d_v, verts)
+    ctx.h2d(d_f, faces)
+    flush_bytes = 512 << 20
+    d_flush = ctx.dev_alloc(flush_bytes)
+    for _ in range(2):
+        fl = sharded_mesh_flags(ctx, full, dist, torch, d_v, nv, d_f, nt)
+    evs = [(ctx.event(), ctx.event()) for _ in range(reps)]
+    for a, b in evs:
+        ctx.memset(d_flush, 0, flush_bytes)
+        ctx.record(a)
+        fl = sharded_mesh_flags(ctx, full, dist, torch, d_v, nv, d_f, nt)
+        ctx.record(b)
+    ctx.sync()
+    ms = float(np.mean([ctx.elapsed_ms(a, b) for a, b in evs]))
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    for a, b in evs:
+        ctx.event_destroy(a)
+        ctx.event_destroy(b)
+    out = None
+    if rank == 0:
+        d_ov, d_of, d_rgb, d_n = ctx.dev_alloc(nt * 72), ctx.dev_alloc(nt * 16), ctx.dev_alloc(nt * 9), ctx.dev_alloc(8)
+        e0, e1 = ctx.event(), ctx.event()
+        ctx.record(e0)
+        ctx.mesh_emit_dev(d_v, nv, d_f, nt, fl.data_ptr(), pcs.RETURN_OUTSIDE, nt, d_ov, d_of, d_rgb, d_n)
+        ctx.record(e1)
+        kept = np.zeros(1, np.uint64)
+        ctx.d2h(kept, d_n)
+        emit_ms = ctx.elapsed_ms(e0, e1)
+        # the same mask on ONE GPU (rank 0 holds the full map): the gathered flags must equal it bit for bit
+        d_one = ctx.dev_alloc(nt)
+        ctx.mesh_contacts_dev(full, d_v, nv, d_f, nt, d_one)
+        one, got = np.empty(nt, np.uint8), np.empty(nt, np.uint8)
+        ctx.d2h(one, d_one)
+        ctx.d2h(got, fl.data_ptr())
+        b_flags = (16 + 24.0 * nv / nt + 1) * nt
+        out = {"triangles": nt, "n_gpus": world, "case": "s~0.5 over the footprint of all ranks' frames",
+               "gathered_map_voxels": n_total, "map_allgather_ms": gather_ms, "flags_ms": ms, "tris_per_s": nt / (ms * 1e-3),
+               "inside_fraction": float(got.mean()), "equals_one_gpu_flags": bool(np.array_equal(one, got)),
+               "emit_on_rank0_ms": emit_ms, "kept_outside": int(kept[0]),
+               "roofline": {"bound": "hbm", "achieved": b_flags / (ms * 1e-3) / 1e9, "peak": peak * world, "unit": "GB/s",
+                            "frac": b_flags / (ms * 1e-3) / 1e9 / (peak * world),
+                            "kernel": "mesh_{vertex,tri,undecided,contacts_big}_kernel per rank + all-gather of the flags",
+                            "note": "58 MB over N GPUs: launch / collective latency bound"}}
+        for p_ in (d_ov, d_of, d_rgb, d_n, d_one):
+            ctx.dev_free(p_)
+    for p_ in (d_v, d_f, d_flush):
+        ctx.dev_free(p_)
+    full.destroy()
     dist.barrier()
     return out
 

@@ -317,6 +317,12 @@ PCS_API int pcs_mesh_mask_dev(pcs_ctx* ctx, pcs_map* map, const double* verts_de
                               uint64_t nt, int mask_type, uint64_t out_cap_tris, double* out_verts_dev,
                               int32_t* out_faces4_dev, uint8_t* out_rgb_dev, uint8_t* tri_flags_dev,
                               uint64_t* n_out_tris_dev);
+/* The output assembly alone, from contact flags that already exist (the multi-GPU mask: every rank decides a range of
+ * triangles, the flags are gathered, one rank emits): same outputs as pcs_mesh_mask_dev.  *n_out_tris_dev receives the
+ * kept count of the compaction (INSIDE / OUTSIDE); it is set to 0 for COLORIZED, which keeps all nt triangles. */
+PCS_API int pcs_mesh_emit_dev(pcs_ctx* ctx, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev, uint64_t nt,
+                              const uint8_t* tri_flags_dev, int mask_type, uint64_t out_cap_tris, double* out_verts_dev,
+                              int32_t* out_faces4_dev, uint8_t* out_rgb_dev, uint64_t* n_out_tris_dev);
 PCS_API int pcs_mesh_contacts_dev(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv,
                                   const int32_t* faces4_dev, uint64_t nt, uint8_t* tri_flags_dev);
 

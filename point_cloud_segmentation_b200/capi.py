@@ -105,6 +105,7 @@ SIGNATURES = {
     "pcs_exchange_barrier_dev": (_i, [_vp, _pp, _pp, _i, C.c_uint32]),
     "pcs_mesh_mask": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _i, _u64, _vp, _vp, _vp, _vp, _pu64, _pu64]),
     "pcs_mesh_mask_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _i, _u64, _vp, _vp, _vp, _vp, _vp]),
+    "pcs_mesh_emit_dev": (_i, [_vp, _vp, _u64, _vp, _u64, _vp, _i, _u64, _vp, _vp, _vp, _vp]),
     "pcs_mesh_contacts_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _u64, _vp]),
     "pcs_synth_frames_dev": (_i, [_vp, _u64, _i, _i, _i, _i, _vp, _vp]),
 }
@@ -522,6 +523,12 @@ class Context:
         _check(self.lib.pcs_mesh_mask_dev(self.h, vmap.h, _p(verts_dev), int(nv), _p(faces4_dev), int(nt), int(mask_type),
                                           int(cap_tris), _p(out_verts_dev), _p(out_faces4_dev), _p(out_rgb_dev), _p(flags_dev),
                                           _p(n_out_dev)))
+
+    def mesh_emit_dev(self, verts_dev: int, nv: int, faces4_dev: int, nt: int, flags_dev: int, mask_type: int, cap_tris: int,
+                      out_verts_dev: int | None, out_faces4_dev: int | None, out_rgb_dev: int | None, n_out_dev: int):
+        """Output assembly from existing contact flags (multi-GPU mask: flags gathered from all ranks)."""
+        _check(self.lib.pcs_mesh_emit_dev(self.h, _p(verts_dev), int(nv), _p(faces4_dev), int(nt), _p(flags_dev), int(mask_type),
+                                          int(cap_tris), _p(out_verts_dev), _p(out_faces4_dev), _p(out_rgb_dev), _p(n_out_dev)))
 
     def mesh_contacts_dev(self, vmap: VoxelMap, verts_dev: int, nv: int, faces4_dev: int, nt: int, flags_dev: int):
         _check(self.lib.pcs_mesh_contacts_dev(self.h, vmap.h, _p(verts_dev), int(nv), _p(faces4_dev), int(nt),

@@ -772,6 +772,26 @@ static int mesh_assemble_dev(pcs_ctx* ctx, const double* d_verts, uint64_t nv, c
   return PCS_OK;
 }
 
+int pcs_mesh_emit_dev(pcs_ctx* ctx, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev, uint64_t nt,
+                      const uint8_t* tri_flags_dev, int mask_type, uint64_t out_cap_tris, double* out_verts_dev,
+                      int32_t* out_faces4_dev, uint8_t* out_rgb_dev, uint64_t* n_out_tris_dev)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(mask_type >= 0 && mask_type <= 2, "Invalid mask type");
+  PCS_CHECK_ARG(nt < (1ull << 31) && nv < (1ull << 31), "mesh too large");
+  PCS_CHECK_ARG(nt == 0 || (verts_dev && faces4_dev && tri_flags_dev), "NULL argument");
+  PCS_CHECK_ARG(((uintptr_t)faces4_dev & 15u) == 0 && ((uintptr_t)out_faces4_dev & 15u) == 0, "faces4 must be 16-byte aligned");
+  PCS_CHECK_ARG(n_out_tris_dev != nullptr && ((uintptr_t)n_out_tris_dev & 7u) == 0, "n_out_tris_dev must be an aligned device pointer");
+  const unsigned long long* d_total = nullptr;
+  PCS_TRY(mesh_assemble_dev(ctx, verts_dev, nv, faces4_dev, nt, tri_flags_dev, mask_type, out_cap_tris, out_verts_dev,
+                            out_faces4_dev, out_rgb_dev, &d_total));
+  if (d_total)
+    PCS_CUDA(cudaMemcpyAsync(n_out_tris_dev, d_total, 8, cudaMemcpyDeviceToDevice, ctx->stream));
+  else
+    PCS_CUDA(cudaMemsetAsync(n_out_tris_dev, 0, 8, ctx->stream));  // COLORIZED (all nt kept) and empty meshes: no compaction ran
+  return PCS_OK;
+}
+
 int pcs_mesh_mask_dev(pcs_ctx* ctx, pcs_map* map, const double* verts_dev, uint64_t nv, const int32_t* faces4_dev, uint64_t nt,
                       int mask_type, uint64_t out_cap_tris, double* out_verts_dev, int32_t* out_faces4_dev,
                       uint8_t* out_rgb_dev, uint8_t* tri_flags_dev, uint64_t* n_out_tris_dev)

@@ -113,24 +113,75 @@ class MapExchange:
 
     def allgather_owned(self, into):
         """Merge every rank's owned slice into `into` (same interface) so that each rank holds the whole map."""
-        torch, dist = self.torch, self.dist
-        n_own = self.owned.size()
-        send = self._buffer("_send", n_own)
-        self.owned.pack_by_owner_into(1, send)
-        sizes = torch.zeros(self.world, dtype=torch.int64, device=self.device)
-        mine = torch.tensor([n_own], dtype=torch.int64, device=self.device)
-        dist.all_gather_into_tensor(sizes, mine)
-        sz = sizes.cpu().numpy().astype(np.int64)
-        mx = int(sz.max()) if sz.size else 0
-        recv = self._buffer("_recv", mx * self.world)
-        padded = send[: 2 * mx] if send.numel() >= 2 * mx else torch.cat(
-            [send, torch.zeros(2 * mx - send.numel(), dtype=torch.int64, device=self.device)])
-        dist.all_gather_into_tensor(recv[: 2 * mx * self.world], padded.contiguous())
-        for r in range(self.world):
-            n = int(sz[r])
-            if n:
-                into.merge_records_from(recv[2 * mx * r: 2 * mx * r + 2 * n], n)
-        return int(sz.sum())
+        n, self._send, self._recv = allgather_map(self.owned, into, self.dist, self.torch, self.device, self._send, self._recv)
+        return n
+
+
+def _grow(torch, cur, n_records: int, device):
+    if cur is None or cur.numel() < 2 * n_records:
+        cur = torch.empty(2 * max(n_records, 1024) * 5 // 4, dtype=torch.int64, device=device)
+    return cur
+
+
+def allgather_map(owned, into, dist, torch, device, send=None, recv=None):
+    """Every rank's `owned` slice (GpuMapAdapter or an object with its interface) merged into `into` on every rank: the
+    gathered map the mesh mask runs on (north_star).  One all-gather of the slice sizes, one all-gather of the
+    16-byte records padded to the largest slice.  Returns (total voxels, send buffer, receive buffer) -- the buffers can be
+    passed back in to avoid reallocation."""
+    world = dist.get_world_size()
+    n_own = owned.size()
+    send = _grow(torch, send, n_own, device)
+    owned.pack_by_owner_into(1, send)
+    sizes = torch.zeros(world, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(sizes, torch.tensor([n_own], dtype=torch.int64, device=device))
+    sz = sizes.cpu().numpy().astype(np.int64)
+    mx = int(sz.max()) if sz.size else 0
+    recv = _grow(torch, recv, mx * world, device)
+    padded = send[: 2 * mx] if send.numel() >= 2 * mx else torch.cat(
+        [send, torch.zeros(2 * mx - send.numel(), dtype=torch.int64, device=device)])
+    dist.all_gather_into_tensor(recv[: 2 * mx * world], padded.contiguous())
+    for r in range(world):
+        n = int(sz[r])
+        if n:
+            into.merge_records_from(recv[2 * mx * r: 2 * mx * r + 2 * n], n)
+    return int(sz.sum()), send, recv
+
+
+def triangle_range(nt: int, world: int, rank: int):
+    """Triangles [lo, hi) of rank `rank`: an even split in input order (the mask's output order is the input order)."""
+    return rank * nt // world, (rank + 1) * nt // world
+
+
+def gather_triangle_flags(dist, torch, device, nt: int, compute_slice):
+    """maskMesh sharded over the ranks (octomap_mesh_masking.cpp:118-283 decides every triangle independently): each rank
+    decides its own range of triangles against the gathered map, the flags are all-gathered, every rank returns the nt
+    flags in input order.  compute_slice(lo, hi, out) must fill out[: hi - lo] (uint8 tensor on `device`) with the contact
+    flags of triangles [lo, hi); on a GPU that is pcs_mesh_contacts_dev on a pointer offset by 16 * lo bytes."""
+    world, rank = dist.get_world_size(), dist.get_rank()
+    width = (nt + world - 1) // world  # longest slice
+    mine = torch.zeros(max(width, 1), dtype=torch.uint8, device=device)
+    lo, hi = triangle_range(nt, world, rank)
+    if hi > lo:
+        compute_slice(lo, hi, mine)
+    allf = torch.empty(world * max(width, 1), dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(allf, mine)
+    if nt % world == 0 and nt > 0:
+        return allf  # every slice has exactly `width` triangles: the gathered buffer is already in input order
+    out = torch.empty(nt, dtype=torch.uint8, device=device)
+    for r in range(world):
+        a, b = triangle_range(nt, world, r)
+        out[a:b] = allf[r * width: r * width + (b - a)]
+    return out
+
+
+def sharded_mesh_flags(ctx, full_map, dist, torch, verts_dev: int, nv: int, faces4_dev: int, nt: int):
+    """The GPU form of gather_triangle_flags: returns a uint8 CUDA tensor of nt flags, identical on every rank."""
+    device = torch.device("cuda", ctx.device)
+
+    def compute(lo, hi, out):
+        ctx.mesh_contacts_dev(full_map, verts_dev, nv, faces4_dev + 16 * lo, hi - lo, out.data_ptr())
+
+    return gather_triangle_flags(dist, torch, device, nt, compute)
 
 
 def _push(ctx, local, owners, clear_local):

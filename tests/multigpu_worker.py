@@ -51,7 +51,36 @@ def main():
     peer.exchange()
     ctx.sync()
     k2, a2, b2, _ = peer.owned_map.export()
-    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), k1=k1, a1=a1, b1=b1, k2=k2, a2=a2, b2=b2, kf=kf, af=af, bf=bf)
+    # sharded mesh mask on the gathered map (peer slices gathered this time): flags + rank 0's emitted OUTSIDE mesh
+    from point_cloud_segmentation_b200.distributed import allgather_map, sharded_mesh_flags
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from util import grid_mesh, surface
+
+    full2 = ctx.create_map(res, cap)
+    allgather_map(peer.owned, GpuMapAdapter(ctx, full2), dist, torch, torch.device("cuda", local_rank))
+    verts, faces = grid_mesh(81, 41, -0.45, 0.45, -0.25, 0.25, surface)
+    faces = np.ascontiguousarray(np.concatenate([faces, faces[:1]]))  # 6643 triangles: not a multiple of 2
+    nv, nt = verts.shape[0], faces.shape[0]
+    d_v, d_f = ctx.dev_alloc(verts.nbytes), ctx.dev_alloc(faces.nbytes)
+    ctx.h2d(d_v, verts)
+    ctx.h2d(d_f, faces)
+    fl = sharded_mesh_flags(ctx, full2, dist, torch, d_v, nv, d_f, nt)
+    ctx.sync()
+    mesh_flags = fl.cpu().numpy()
+    emitted = {}
+    if rank == 0:
+        d_ov, d_of, d_rgb, d_n = ctx.dev_alloc(nt * 72), ctx.dev_alloc(nt * 16), ctx.dev_alloc(nt * 9), ctx.dev_alloc(8)
+        ctx.mesh_emit_dev(d_v, nv, d_f, nt, fl.data_ptr(), pcs.RETURN_OUTSIDE, nt, d_ov, d_of, d_rgb, d_n)
+        n_out = np.zeros(1, np.uint64)
+        ctx.d2h(n_out, d_n)
+        k = int(n_out[0])
+        ov, of = np.empty((3 * k, 3), np.float64), np.empty((k, 4), np.int32)
+        ctx.d2h(ov, d_ov)
+        ctx.d2h(of, d_of)
+        emitted = dict(ov=ov, of=of)
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), k1=k1, a1=a1, b1=b1, k2=k2, a2=a2, b2=b2, kf=kf, af=af, bf=bf,
+             mesh_flags=mesh_flags, **emitted)
     peer.close()
     dist.barrier()
     dist.destroy_process_group()

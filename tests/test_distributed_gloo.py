@@ -46,6 +46,7 @@ class NumpyMap:
 
 def _worker(rank, world, port, out_dir):
     sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
     import torch
     import torch.distributed as dist
 
@@ -67,9 +68,23 @@ def _worker(rank, world, port, out_dir):
     ex.exchange()  # idempotent with clear_owned
     total = ex.allgather_owned(full)
     keys = np.array(sorted(full.recs), np.uint64)
+    # sharded mesh mask on the gathered map: each rank decides its range of triangles (the oracle stands in for the
+    # kernel), the flags are gathered; nt = 101 is not a multiple of the world size
+    from point_cloud_segmentation_b200.distributed import gather_triangle_flags, triangle_range
+    from util import grid_mesh, surface
+
+    verts, faces = grid_mesh(10, 5, -0.45, 0.45, -0.25, 0.25, surface)
+    faces = np.concatenate([faces, faces[:1]])
+    occ = np.array([k for k in keys if (full.recs[int(k)] >> 32) > 0], np.uint64)
+
+    def compute(lo, hi, out):
+        out[: hi - lo] = torch.from_numpy(O.mesh_contacts_keys(occ, res, verts, faces[lo:hi]))
+
+    flags = gather_triangle_flags(dist, torch, torch.device("cpu"), faces.shape[0], compute).numpy()
+    assert triangle_range(101, world, 0) == (0, 50) and triangle_range(101, world, 1) == (50, 101)
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), keys=keys,
              counts=np.array([full.recs[int(k)] for k in keys], np.uint64), owned=np.array(sorted(owned.recs), np.uint64),
-             total=total)
+             total=total, flags=flags)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -99,5 +114,14 @@ def test_exchange_world2_gloo(O, tmp_path):
     for o in outs:  # after the all-gather every rank holds the map a single GPU would have built
         assert np.array_equal(o["keys"], keys) and np.array_equal(o["counts"], counts)
         assert int(o["total"]) == keys.size
+    # the sharded mask equals the one-process mask, flag for flag, on every rank
+    from util import grid_mesh, surface
+
+    verts, faces = grid_mesh(10, 5, -0.45, 0.45, -0.25, 0.25, surface)
+    faces = np.concatenate([faces, faces[:1]])
+    want = O.mesh_contacts_keys(keys[(counts >> np.uint64(32)) > 0], res, verts, faces)
+    assert 0 < want.sum() < want.size
+    for o in outs:
+        assert np.array_equal(o["flags"], want)
     owned = np.concatenate([o["owned"] for o in outs])
     assert owned.size == keys.size and np.array_equal(np.sort(owned), keys)  # slices partition the map

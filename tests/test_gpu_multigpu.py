@@ -46,6 +46,16 @@ def test_exchange_world2_nccl_and_peer_memory(ctx, pcs, tmp_path):
             assert np.array_equal(o["k" + tag], keys[mine]), (r, tag)
             assert np.array_equal(o["a" + tag], c0[mine]) and np.array_equal(o["b" + tag], c1[mine]), (r, tag)
         assert np.array_equal(o["kf"], keys) and np.array_equal(o["af"], c0) and np.array_equal(o["bf"], c1)
+    # sharded mesh mask == the one-GPU mask, flag for flag on every rank; rank 0's emitted mesh == the host call's
+    from util import grid_mesh, surface
+
+    verts, faces = grid_mesh(81, 41, -0.45, 0.45, -0.25, 0.25, surface)
+    faces = np.ascontiguousarray(np.concatenate([faces, faces[:1]]))
+    ov, of, _, flags = ctx.mesh_mask(ref, verts, faces, pcs.RETURN_OUTSIDE)
+    assert 0 < flags.sum() < flags.size
+    for o in outs:
+        assert np.array_equal(o["mesh_flags"], flags)
+    assert outs[0]["ov"].tobytes() == ov.tobytes() and np.array_equal(outs[0]["of"], of)
     ref.destroy()
     ctx.dev_free(d_pose)
     ctx.dev_free(d_in)
