@@ -93,3 +93,58 @@ def test_cmake_project_configures_with_reference_target_names(tmp_path):
                 "pcs_scan_integration_octomap_mesh_masking"):
         assert tgt in text
     assert "NAMESPACE pcs::" in text and "CMAKE_CUDA_ARCHITECTURES 100a" in text
+
+
+def test_cmake_packages_are_found_by_a_reference_style_consumer(built, tmp_path):
+    """The drop-in claim of INTEGRATION.md section 4: a consumer that does exactly what pcs_ros/CMakeLists.txt:6-7,48-64
+    does -- find_package(pcs_scan_integration REQUIRED), find_package(pcs_detection REQUIRED), link the pcs:: targets --
+    configures, compiles and links against an install prefix of this repository.  (libpcs_b200.so itself is the one the
+    Python-driven build made: cmake --install only copies files, so the CUDA sources are not compiled a second time.)"""
+    import shutil
+    import subprocess
+
+    if not shutil.which("cmake") or not shutil.which("nvcc"):
+        pytest.skip("cmake / nvcc not available")
+    from point_cloud_segmentation_b200 import _build
+
+    build, prefix, consumer = tmp_path / "build", tmp_path / "prefix", tmp_path / "consumer"
+    r = subprocess.run(["cmake", "-S", ROOT, "-B", str(build)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    shutil.copy(_build.LIB_PATH, build / "libpcs_b200.so")
+    r = subprocess.run(["cmake", "--install", str(build), "--prefix", str(prefix)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    for pkg in ("pcs_b200", "pcs_detection", "pcs_scan_integration"):
+        for f in (f"{pkg}-config.cmake", f"{pkg}-config-version.cmake", f"{pkg}-targets.cmake"):
+            assert (prefix / "lib" / "cmake" / pkg / f).exists(), (pkg, f)
+    consumer.mkdir()
+    (consumer / "CMakeLists.txt").write_text("""cmake_minimum_required(VERSION 3.5.0)
+project(pcs_ros_like CXX)
+find_package(pcs_scan_integration REQUIRED)
+find_package(pcs_detection REQUIRED)
+add_executable(node node.cpp)
+target_link_libraries(node pcs::pcs_detection_point_cloud_annotator pcs::pcs_detection_hsv_thresholding
+                      pcs::pcs_scan_integration_octomap_mesh_masking)
+set_target_properties(node PROPERTIES CXX_STANDARD 17)
+""")
+    (consumer / "node.cpp").write_text("""#include <pcs_detection/hsv_thresholding.h>
+#include <pcs_detection/point_cloud_annotator.h>
+#include <pcs_detection/utils.h>
+#include <pcs_scan_integration/octomap_mesh_masking.h>
+int main()
+{
+  pcs_scan_integration::OctomapMeshMask masker;
+  pcs_compat::Mat a(1, 1, pcs_compat::CV_8UC1), b(1, 1, pcs_compat::CV_8UC1), c;
+  a.data[0] = 3;
+  b.data[0] = 5;
+  return pcs_detection::applyMask(a, b, c) && c.data[0] == 15 && pcs_version() == PCS_VERSION ? 0 : 1;
+}
+""")
+    cb = tmp_path / "consumer_build"
+    r = subprocess.run(["cmake", "-S", str(consumer), "-B", str(cb), f"-DCMAKE_PREFIX_PATH={prefix}"], capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    r = subprocess.run(["cmake", "--build", str(cb)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    env = dict(os.environ, LD_LIBRARY_PATH=str(prefix / "lib") + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    r = subprocess.run([str(cb / "node")], capture_output=True, text=True, timeout=60, env=env)
+    assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-1000:]  # applyMask and pcs_version need no GPU
