@@ -96,6 +96,17 @@ typedef struct pcs_stats
   uint64_t bytes_h2d, bytes_d2h;
 } pcs_stats;
 
+/* Counters of a voxel map: what the scan has put into it so far. */
+typedef struct pcs_map_stats
+{
+  uint64_t voxels;          /* distinct voxels touched */
+  uint64_t occupied;        /* voxels with count1 >= 1: the leaves of the reference octree */
+  uint64_t points_rejected; /* sum of count0: finite in-range points that failed colorPassthrough */
+  uint64_t points_labelled; /* sum of count1: points the reference would have inserted into the octree */
+  uint64_t table_slots;     /* size of the hash table */
+  double load_factor;       /* voxels / table_slots */
+} pcs_map_stats;
+
 typedef struct pcs_ctx pcs_ctx;
 typedef struct pcs_map pcs_map;
 
@@ -240,6 +251,8 @@ PCS_API int pcs_map_integrate_dev(pcs_ctx* ctx, pcs_map* map, const pcs_point_xy
                                   const float* pose_dev, int lower, int upper, int limit_negative);
 /* number of voxels touched / occupied (count1 >= 1); PCS_ERR_CAPACITY if the table overflowed at any point */
 PCS_API int pcs_map_size(pcs_ctx* ctx, pcs_map* map, uint64_t* n_voxels, uint64_t* n_occupied);
+/* finite / labelled point counts, voxels touched and occupied, hash load factor (one pass over the live voxels) */
+PCS_API int pcs_map_get_stats(pcs_ctx* ctx, pcs_map* map, pcs_map_stats* out);
 /* Export in octree (Morton / child-index DFS) order: key48, the two counters and the float log-odds the reference
  * tree would hold (0 for voxels with count1 == 0).  Any output pointer may be NULL.  If cap < n only `n` is
  * reported and PCS_ERR_CAPACITY returned (two-call size query). */

@@ -15,6 +15,33 @@
  *            bit0/bit1 = 1/0 free leaf, 0/1 occupied leaf, 1/1 inner, 0/0 unknown)
  * PARITY UNPINNED by the reference for keys/log-odds/prune (octomap_mesh_masking_unit.cpp:59-70 checks non-null
  * only); the .bt codec is pinned by a byte-exact round trip of the reference fixture box_2m.bt.
+ *
+ * Derivation, rule by rule (upstream function -> the expression restated here; upstream = octomap 1.9.x / tesseract
+ * 0.1-era headers as remembered, neither is on this machine, so none of this can be re-read offline):
+ *   resolution_factor   OcTreeBaseImpl::setResolution:      resolution_factor = 1. / resolution            (double)
+ *   key                 OcTreeBaseImpl::coordToKeyChecked:  int scaled = ((int) floor(resolution_factor * coordinate)) +
+ *                       tree_max_val; valid iff scaled >= 0 && (unsigned) scaled < 2 * tree_max_val; the float coordinate of a
+ *                       pcl point is promoted to double first (updateNode(double x, double y, double z, bool))
+ *                       -> orc_coord_to_key: floor(inv_res * (double)x) + 32768, product rounded once in double
+ *                       (tests/test_oracle_keys.py enumerates every voxel boundary of three resolutions against exact
+ *                       rational arithmetic, for this file and, in test_gpu_keys.py, for the CUDA path)
+ *   hit / clamp values  octomap_utils.h logodds(double p) = (float) log(p / (1 - p)): DOUBLE log, then one cast to float;
+ *                       AbstractOccupancyOcTree(): setProbHit(0.7), setClampingThresMax(0.971), setClampingThresMin(0.1192)
+ *                       -> 0x3f58e883 and 0x4060b4ba; evaluating in float (logf) would give 0x3f58e882 / 0x4060b4bc,
+ *                       which tests/test_oracle_keys.py shows is NOT what the LUT of the CUDA path holds
+ *   leaf update         OccupancyOcTreeBase::updateNodeLogOdds: node->addValue(update) (float +=); if (< clamping_thres_min)
+ *                       set min and return; if (> clamping_thres_max) set max  -> hits only: 0x3f58e883, 0x3fd8e883,
+ *                       0x4022ae62, 0x4058e883, then 0x4060b4ba for ever
+ *   early return        OccupancyOcTreeBase::updateNode(key, float log_odds_update, lazy): leaf = search(key); if (leaf &&
+ *                       log_odds_update >= 0 && leaf->getLogOdds() >= clamping_thres_max) return leaf
+ *   inner nodes         updateNodeRecurs: after the child returns, if (pruneNode(node)) ... else node->updateOccupancyChildren()
+ *                       (= max of the children's log-odds); pruneNode needs 8 existing, childless, equal-valued children
+ *   tesseract           tesseract_geometry::Octree(cloud, resolution, sub_type, prune): new octomap::OcTree(resolution); for each
+ *                       point updateNode(x, y, z, true); then, if prune, tesseract's own prune(): an inner node whose 8
+ *                       children are leaves ABOVE the occupancy threshold collapses (values need not be equal, the parent
+ *                       keeps child 0's value) -> orc_octree_finalize_tesseract
+ * What stays unpinned after the tests above: that these remembered expressions ARE upstream's (in particular tesseract's
+ * prune rule and the early return), and the operation order of pcl::transformPointCloud (oracle/cloud.c).
  * This tree is also the timed CPU baseline for integration (16-level pointer descent, `malloc` per node).
  */
 #include "pcs_oracle.h"

@@ -45,6 +45,11 @@ class Stats(C.Structure):
                 ("bytes_d2h", C.c_uint64)]
 
 
+class MapStats(C.Structure):
+    _fields_ = [("voxels", C.c_uint64), ("occupied", C.c_uint64), ("points_rejected", C.c_uint64),
+                ("points_labelled", C.c_uint64), ("table_slots", C.c_uint64), ("load_factor", C.c_double)]
+
+
 _vp, _sz, _i, _u64, _dbl = C.c_void_p, C.c_size_t, C.c_int, C.c_uint64, C.c_double
 _pp = C.POINTER(C.c_void_p)
 _pu64 = C.POINTER(C.c_uint64)
@@ -89,6 +94,7 @@ SIGNATURES = {
     "pcs_map_integrate": (_i, [_vp, _vp, _vp, _u64, _vp, _i, _i, _i]),
     "pcs_map_integrate_dev": (_i, [_vp, _vp, _vp, _u64, _vp, _i, _i, _i]),
     "pcs_map_size": (_i, [_vp, _vp, _pu64, _pu64]),
+    "pcs_map_get_stats": (_i, [_vp, _vp, C.POINTER(MapStats)]),
     "pcs_map_export": (_i, [_vp, _vp, _u64, _vp, _vp, _vp, _vp, _pu64]),
     "pcs_map_write_bt": (_i, [_vp, _vp, _vp, _u64, _pu64]),
     "pcs_map_leaf_centers": (_i, [_vp, _vp, _u64, _vp, _pu64]),
@@ -238,6 +244,11 @@ class VoxelMap:
         nv, no = C.c_uint64(0), C.c_uint64(0)
         _check(self.ctx.lib.pcs_map_size(self.ctx.h, self.h, C.byref(nv), C.byref(no)))
         return int(nv.value), int(no.value)
+
+    def stats(self) -> dict:
+        st = MapStats()
+        _check(self.ctx.lib.pcs_map_get_stats(self.ctx.h, self.h, C.byref(st)))
+        return {f: getattr(st, f) for f, _ in MapStats._fields_}
 
     def export(self):
         """(key48, count0, count1, logodds) in Morton order."""

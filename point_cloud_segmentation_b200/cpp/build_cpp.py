@@ -37,5 +37,27 @@ def build(force: bool = False) -> list[str]:
     return outs
 
 
+def build_pybind(force: bool = False) -> str:
+    """The pybind11 module for the Python detection scripts: cpp/pybind/pcs_detection_py.cpp -> pcs_detection_py.<abi>.so
+    next to libpcs_b200.so (found through an $ORIGIN rpath).  Needs the Python headers and pybind11."""
+    import sysconfig
+
+    import pybind11
+
+    lib = os.path.join(_PKG, "libpcs_b200.so")
+    src = os.path.join(_HERE, "pybind", "pcs_detection_py.cpp")
+    out = os.path.join(_PKG, "pcs_detection_py" + sysconfig.get_config_var("EXT_SUFFIX"))
+    hdr = os.path.join(_ROOT, "include", "pcs_b200.h")
+    if not force and os.path.exists(out) and os.path.getmtime(out) >= max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        return out
+    cmd = ["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-fvisibility=hidden", "-I", sysconfig.get_paths()["include"],
+           "-I", pybind11.get_include(), "-I", os.path.join(_ROOT, "include"), src, "-o", out, lib, "-Wl,-rpath,$ORIGIN"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"g++ failed for the pybind11 module:\n{res.stdout}\n{res.stderr}")
+    return out
+
+
 if __name__ == "__main__":
     print("\n".join(build(force=True)))
+    print(build_pybind(force=True))

@@ -77,6 +77,32 @@ __global__ void map_count_occupied_kernel(MapView m, unsigned int* __restrict__ 
     atomicAdd(n_occ, mine);
 }
 
+// [0] occupied voxels, [1] sum of count0, [2] sum of count1 over the live voxels
+__global__ void map_stats_kernel(MapView m, unsigned long long* __restrict__ acc)
+{
+  const unsigned int n = *m.n_used;
+  unsigned long long occ = 0, s0 = 0, s1 = 0;
+  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+  {
+    const unsigned long long c = m.slots[m.live[i]].counts;
+    s0 += c & 0xffffffffull;
+    s1 += c >> 32;
+    occ += (c >> 32) ? 1ull : 0ull;
+  }
+  for (int o = 16; o > 0; o >>= 1)
+  {
+    occ += __shfl_xor_sync(0xffffffffu, occ, o);
+    s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+  }
+  if ((threadIdx.x & 31) == 0 && (s0 | s1))
+  {
+    atomicAdd(&acc[0], occ);
+    atomicAdd(&acc[1], s0);
+    atomicAdd(&acc[2], s1);
+  }
+}
+
 // after the sort: idx[i] = position of the i-th record in Morton order
 __global__ void map_emit_kernel(const Record* __restrict__ recs, const unsigned int* __restrict__ idx, unsigned int n,
                                 unsigned long long* __restrict__ key48, unsigned int* __restrict__ c0,
@@ -427,6 +453,33 @@ int pcs_map_size(pcs_ctx* ctx, pcs_map* map, uint64_t* n_voxels, uint64_t* n_occ
   PCS_TRY(read_counters(ctx, map, c));
   if (n_voxels)
     *n_voxels = c[0];
+  return PCS_OK;
+}
+
+int pcs_map_get_stats(pcs_ctx* ctx, pcs_map* map, pcs_map_stats* out)
+{
+  PCS_TRY(ctx_bind(ctx));
+  PCS_CHECK_ARG(map && out, "NULL argument");
+  memset(out, 0, sizeof(*out));
+  void* scr = nullptr;
+  PCS_TRY(ctx_scratch(ctx, 64, &scr));
+  unsigned long long* acc = (unsigned long long*)scr;
+  PCS_CUDA(cudaMemsetAsync(acc, 0, 32, ctx->stream));
+  map_stats_kernel<<<(unsigned int)ctx->sm_count * 2u, 256, 0, ctx->stream>>>(map->view, acc);
+  count_launch(ctx);
+  PCS_TRY(check_launch("map_stats_kernel"));
+  void* h = nullptr;
+  PCS_TRY(ctx_pinned(ctx, 128, &h));
+  PCS_CUDA(cudaMemcpyAsync((char*)h + 64, acc, 32, cudaMemcpyDeviceToHost, ctx->stream));  // read_counters uses the first bytes
+  unsigned int c[2];
+  PCS_TRY(read_counters(ctx, map, c));  // synchronises the stream
+  const unsigned long long* v = (const unsigned long long*)((char*)h + 64);
+  out->voxels = c[0];
+  out->occupied = v[0];
+  out->points_rejected = v[1];
+  out->points_labelled = v[2];
+  out->table_slots = map->n_slots;
+  out->load_factor = (double)c[0] / (double)map->n_slots;
   return PCS_OK;
 }
 

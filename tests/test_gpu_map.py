@@ -166,3 +166,21 @@ def test_push_to_owners_partitions_the_map(ctx, pcs, O):
     a.destroy()
     b.destroy()
     local.destroy()
+
+
+def test_map_stats_counters(ctx, pcs, O):
+    """pcs_map_get_stats: voxels touched / occupied, rejected and labelled point counts, load factor."""
+    rng = np.random.default_rng(31)
+    cloud = random_cloud(pcs.POINT_DTYPE, 50000, rng, extent=0.5)
+    vmap = ctx.create_map(0.02, 1 << 16)
+    vmap.integrate(cloud, None, 0, 128)
+    keys, c0, c1, _ = vmap.export()
+    st = vmap.stats()
+    assert st["voxels"] == keys.size and st["occupied"] == int((c1 > 0).sum())
+    assert st["points_rejected"] == int(c0.sum()) and st["points_labelled"] == int(c1.sum())
+    assert st["table_slots"] == 1 << 17 and abs(st["load_factor"] - keys.size / (1 << 17)) < 1e-12
+    o_k, o_c0, o_c1 = O.count_voxels(cloud, 0.02, None, 0, 128)
+    assert st["points_labelled"] == int(o_c1.sum()) and st["points_rejected"] == int(o_c0.sum())
+    vmap.clear()
+    assert vmap.stats()["voxels"] == 0 and vmap.stats()["points_labelled"] == 0
+    vmap.destroy()

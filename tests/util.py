@@ -64,3 +64,33 @@ def random_cloud(point_dtype, n, rng, extent=1.0, nan_frac=0.05, inf_frac=0.01):
 
 def same_bytes(a: np.ndarray, b: np.ndarray) -> bool:
     return a.shape == b.shape and a.tobytes() == b.tobytes()
+
+
+def key_boundary_cloud(point_dtype, res: float):
+    """Points on the x axis at every voxel boundary k * res of the 16-bit key range (float32), one float32 ulp below and
+    above each, and a few beyond both ends of the range (those must be culled)."""
+    k = np.arange(-32768 - 2, 32768 + 3, dtype=np.float64)
+    x = (k * res).astype(np.float32)
+    xs = np.concatenate([x, np.nextafter(x, np.float32(-np.inf)), np.nextafter(x, np.float32(np.inf))])
+    c = np.zeros(xs.size, point_dtype)
+    c["x"] = xs
+    c["r"] = c["g"] = c["b"] = 255
+    c[point_dtype.names[3]] = 1.0
+    return c
+
+
+def expected_key_histogram(xs: np.ndarray, res: float):
+    """Exact evaluation of octomap's coordToKeyChecked for float32 coordinates: floor(RN64(fl64(1 / res) * x)) + 32768,
+    kept iff in [0, 65536).  Returns (sorted keys, counts)."""
+    from fractions import Fraction
+    import math
+
+    inv = Fraction(1.0 / res)  # the double the library computes once per map
+    hist = {}
+    for x in xs.tolist():
+        p = float(inv * Fraction(x))  # float(Fraction) rounds to nearest even: the single rounding of the double product
+        k = math.floor(p) + 32768
+        if 0 <= k < 65536:
+            hist[k] = hist.get(k, 0) + 1
+    keys = np.array(sorted(hist), np.uint64)
+    return keys, np.array([hist[int(q)] for q in keys], np.uint64)
