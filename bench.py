@@ -54,7 +54,7 @@ def make_config(workload: str, world: int, exchange_kind: str | None = "peer") -
     partition = "single GPU"
     if world > 1:
         partition = ("frames sharded by rank, voxel owner = mix64(key48) % n_gpus, exchange = " +
-                     ("one push kernel over NVLink peer memory (CUDA IPC)" if exchange_kind == "peer"
+                     ("push kernel over NVLink peer memory (CUDA IPC)" if exchange_kind == "peer"
                       else "NCCL all-to-all of 16-byte records"))
     return {"workload": workload, "frames_per_gpu": frames_per_gpu, "width": w, "height": h, "voxel_resolution_m": res,
             "label_filter": "lower=255 upper=255", "outputs": "annotated cloud + mask + voxel map",
@@ -210,10 +210,12 @@ class Exchanger:
                     self.side = torch.cuda.Stream()
                     self.ctx_x = pcs.Context(local_rank, self.side.cuda_stream)
                     with torch.cuda.stream(self.side):
-                        self.exch = PeerMapExchange(self.ctx_x, vmap, dist, torch, cap, barrier=args.barrier, clear_local=True)
+                        self.exch = PeerMapExchange(self.ctx_x, vmap, dist, torch, cap, barrier=args.barrier, clear_local=True,
+                                                    mode=args.peer_mode)
                     self.pipelined = True
                 else:
-                    self.exch = PeerMapExchange(ctx, vmap, dist, torch, cap, barrier=args.barrier, clear_local=True)
+                    self.exch = PeerMapExchange(ctx, vmap, dist, torch, cap, barrier=args.barrier, clear_local=True,
+                                                mode=args.peer_mode)
             except Exception as e:  # CUDA IPC unavailable on this box: the NCCL-record form gives the same result
                 print(f"[rank {rank}] peer-memory exchange unavailable ({e}); using NCCL records", file=sys.stderr)
                 self.kind, self.pipelined = "nccl", False
@@ -301,6 +303,8 @@ def main():
     ap.add_argument("--barrier", default="kernel", choices=["kernel", "flags", "allreduce"],
                     help="barrier of the peer exchange: epoch words in peer memory signalled and awaited by one small kernel, "
                          "or by stream memory operations, or a 4-byte NCCL all-reduce")
+    ap.add_argument("--peer-mode", default="mailbox", choices=["mailbox", "atomics"],
+                    help="peer exchange: records stored into the owners' inboxes and merged locally, or remote atomics")
     ap.add_argument("--no-pipeline", action="store_true",
                     help="peer exchange in line on the main stream instead of overlapped with the next scan's kernel")
     ap.add_argument("--exchange-debug", default="", choices=["", "setup-only", "barriers-only"], help=argparse.SUPPRESS)
@@ -535,6 +539,7 @@ def main():
         }
         if exch is not None and exch.kind == "peer":
             line["config"]["exchange_barrier"] = exch.barrier_kind
+            line["config"]["exchange_mode"] = getattr(exch.exch, "mode", None)
             line["config"]["exchange_overlap"] = ("exchange of scan k on a side stream while the kernel of scan k+1 runs "
                                                   "(two local maps)") if exch.pipelined else "in line after every kernel"
         for k, v in (("exchange_check", exchange_check), ("mesh_mask", mesh), ("detector", detector), ("config1", config1),

@@ -290,6 +290,21 @@ PCS_API int pcs_map_ipc_open(pcs_ctx* ctx, const void* handle128, double resolut
                              pcs_map** peer_map);
 PCS_API int pcs_map_push_to_owners_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* const* owners, int n_owners,
                                        int clear_local);
+/* Mailbox form of the same exchange (default of distributed.PeerMapExchange): nothing atomic crosses NVLink.  Every rank
+ * owns, per owned map, an INBOX of pcs_map_inbox_bytes(capacity, n) bytes (a 256-byte header of per-source record counts,
+ * then one segment of `seg_capacity` 16-byte records per source rank) that its peers map through pcs_ipc_export_dev /
+ * pcs_ipc_open_dev.  pcs_map_push_mailbox_dev adds the voxels this rank owns to `own` with local atomics and stores every
+ * other voxel as a record into this rank's segment of its owner's inbox (peer_inboxes[o], o != rank; posted stores, slots
+ * from a local cursor), then publishes the counts.  After the barrier pcs_map_merge_inbox_dev adds the records of the own
+ * inbox to `own`.  An inbox may be written again only after its owner has merged it: alternate two, like the owned maps. */
+PCS_API uint64_t pcs_map_inbox_bytes(uint64_t capacity_voxels, int n_owners);
+PCS_API int pcs_ipc_export_dev(pcs_ctx* ctx, void* dptr, void* handle64);
+PCS_API int pcs_ipc_open_dev(pcs_ctx* ctx, const void* handle64, void** dptr);
+PCS_API int pcs_ipc_close_dev(pcs_ctx* ctx, void* dptr);
+PCS_API int pcs_map_push_mailbox_dev(pcs_ctx* ctx, pcs_map* local, pcs_map* own, int rank, int n_owners,
+                                     void* const* peer_inboxes, uint64_t seg_capacity, int clear_local);
+PCS_API int pcs_map_merge_inbox_dev(pcs_ctx* ctx, pcs_map* own, const void* inbox, int rank, int n_owners,
+                                    uint64_t seg_capacity);
 /* The barrier of that exchange without a collective (no counterpart in the reference, which is single-process): every map
  * carries 16 epoch words that clears do not touch.  After its push, rank r writes the epoch number into word r of every
  * peer's owned map with pcs_stream_write_u32_dev (cuStreamWriteValue32: ordered after the push in the context's stream)

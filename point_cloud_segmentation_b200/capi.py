@@ -105,6 +105,12 @@ SIGNATURES = {
     "pcs_map_ipc_export": (_i, [_vp, _vp, _vp]),
     "pcs_map_ipc_open": (_i, [_vp, _vp, _dbl, _u64, _pp]),
     "pcs_map_push_to_owners_dev": (_i, [_vp, _vp, _pp, _i, _i]),
+    "pcs_map_inbox_bytes": (_u64, [_u64, _i]),
+    "pcs_ipc_export_dev": (_i, [_vp, _vp, _vp]),
+    "pcs_ipc_open_dev": (_i, [_vp, _vp, _pp]),
+    "pcs_ipc_close_dev": (_i, [_vp, _vp]),
+    "pcs_map_push_mailbox_dev": (_i, [_vp, _vp, _vp, _i, _i, _pp, _u64, _i]),
+    "pcs_map_merge_inbox_dev": (_i, [_vp, _vp, _vp, _i, _i, _u64]),
     "pcs_map_epoch_flag_dev": (_i, [_vp, _i, _pp]),
     "pcs_stream_write_u32_dev": (_i, [_vp, _vp, C.c_uint32]),
     "pcs_stream_wait_geq_u32_dev": (_i, [_vp, _vp, C.c_uint32]),
@@ -370,6 +376,29 @@ class Context:
 
     def memset(self, dptr: int, value: int, nbytes: int):
         _check(self.lib.pcs_memset_dev(self.h, _p(dptr), int(value), int(nbytes)))
+
+    def ipc_export(self, dptr: int) -> bytes:
+        buf = (C.c_uint8 * 64)()
+        _check(self.lib.pcs_ipc_export_dev(self.h, _p(dptr), buf))
+        return bytes(buf)
+
+    def ipc_open(self, handle: bytes) -> int:
+        buf = (C.c_uint8 * 64).from_buffer_copy(handle)
+        d = C.c_void_p()
+        _check(self.lib.pcs_ipc_open_dev(self.h, buf, C.byref(d)))
+        return int(d.value)
+
+    def ipc_close(self, dptr: int):
+        _check(self.lib.pcs_ipc_close_dev(self.h, _p(dptr)))
+
+    def push_mailbox(self, local: "VoxelMap", own: "VoxelMap", rank: int, peer_inboxes: "list[int]", seg_capacity: int,
+                     clear_local: bool):
+        arr = (C.c_void_p * len(peer_inboxes))(*[(p or None) for p in peer_inboxes])
+        _check(self.lib.pcs_map_push_mailbox_dev(self.h, local.h, own.h, int(rank), len(peer_inboxes), arr, int(seg_capacity),
+                                                 int(clear_local)))
+
+    def merge_inbox(self, own: "VoxelMap", inbox: int, rank: int, n_owners: int, seg_capacity: int):
+        _check(self.lib.pcs_map_merge_inbox_dev(self.h, own.h, _p(inbox), int(rank), int(n_owners), int(seg_capacity)))
 
     def stream_write_u32(self, flag_dev: int, value: int):
         _check(self.lib.pcs_stream_write_u32_dev(self.h, _p(flag_dev), int(value) & 0xFFFFFFFF))

@@ -202,6 +202,55 @@ __device__ __forceinline__ void map_add(const MapView& m, unsigned long long key
   *m.overflow = 1u;
 }
 
+// Insert for kernels whose threads mostly CLAIM new slots (merging records into an empty table): the claim is reported
+// instead of being appended to the live list, and live_append_warp() appends all claims of a warp with ONE atomic on
+// n_used -- a returning atomic per voxel on that single address serialises (~1 ns each) and dominated those kernels.
+__device__ __forceinline__ bool map_add_claim(const MapView& m, unsigned long long key48, unsigned long long add,
+                                              unsigned int* slot_out)
+{
+  const unsigned long long want = key48 | kValidBit;
+  unsigned long long slot = slot_hash(key48) & m.mask;
+#pragma unroll 1
+  for (unsigned int probe = 0; probe < 65536u; ++probe)
+  {
+    Slot* s = m.slots + slot;
+    unsigned long long k = ld_relaxed_u64(&s->key);
+    bool claimed = false;
+    if (k == 0ull)
+    {
+      k = atomicCAS(&s->key, 0ull, want);
+      claimed = (k == 0ull);
+      if (claimed)
+        k = want;
+    }
+    if (k == want)
+    {
+      atomicAdd(&s->counts, add);
+      *slot_out = (unsigned int)slot;
+      return claimed;
+    }
+    slot = (slot + 1) & m.mask;
+  }
+  *m.overflow = 1u;
+  return false;
+}
+
+// all 32 lanes must call this (converged); `claimed` lanes get consecutive live-list positions from one atomic
+__device__ __forceinline__ void live_append_warp(const MapView& m, bool claimed, unsigned int slot)
+{
+  const unsigned int grp = __ballot_sync(0xffffffffu, claimed);
+  if (!grp)
+    return;
+  const unsigned int lane = threadIdx.x & 31u;
+  const int leader = __ffs(grp) - 1;
+  unsigned int base = 0;
+  if ((int)lane == leader)
+    base = atomicAdd(m.n_used, (unsigned int)__popc(grp));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (claimed)
+    m.live[base + __popc(grp & ((1u << lane) - 1u))] = slot;
+}
+
 // warp-aggregated insert: lanes of `valid` points with equal keys elect a leader that adds the group's counts once
 __device__ __forceinline__ void map_add_warp(const MapView& m, bool valid, unsigned long long key48, bool cls1)
 {

@@ -195,7 +195,13 @@ def _push(ctx, local, owners, clear_local):
 
 
 class PeerMapExchange:
-    """Owner-partitioned reduction through peer memory: local voxels are pushed into the owners' tables by one kernel.
+    """Owner-partitioned reduction through peer memory: local voxels are pushed to their owners by one kernel.
+
+    mode="mailbox" (default): the push kernel stores 16-byte records into the owners' inboxes (plain posted stores over
+    NVLink, slots from local cursors) and adds the voxels it owns itself to its own table; after the barrier each owner
+    merges its inbox with local atomics.  mode="atomics": the push kernel adds straight into the owners' tables with
+    system-scope CAS / RED -- one launch less, but remote atomics cost ~1 us per thousand voxels and collapse when several
+    ranks update the same voxels (overlapping scans).
 
     Set-up (once): every rank creates TWO owned tables, exports their CUDA IPC handles, the handles are all-gathered and
     each rank opens its peers' tables.  exchange() number e: clear the table of the other parity (it held the result of
@@ -212,9 +218,13 @@ class PeerMapExchange:
     the fallback when the driver refuses the stream memory operations on IPC memory.  `owned_map` is the table holding the
     latest result; it stays valid until the next exchange() call."""
 
-    def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int, barrier: str = "kernel", clear_local: bool = False):
+    def __init__(self, ctx, vmap, dist, torch, capacity_voxels: int, barrier: str = "kernel", clear_local: bool = False,
+                 mode: str = "mailbox"):
         from . import capi
 
+        assert mode in ("mailbox", "atomics")
+        self.mode = mode  # mailbox: records stored into the owners' inboxes, merged locally; atomics: remote CAS / RED
+        self.capacity = int(capacity_voxels)
         self.clear_local = clear_local  # the push kernel leaves the local map empty (saves the caller's clear)
         check_shared_stream(ctx, torch)
         self.ctx, self.local, self.dist, self.torch = ctx, vmap, dist, torch
@@ -236,6 +246,22 @@ class PeerMapExchange:
                 else:
                     h = allh[256 * r + 128 * b: 256 * r + 128 * (b + 1)]
                     self._owners[b].append(capi.VoxelMap.ipc_open(ctx, h, vmap.resolution, capacity_voxels))
+        # mailbox mode: one inbox per parity on every rank, mapped by all peers
+        self._inbox, self._peer_inbox = [None, None], [[], []]
+        if mode == "mailbox":
+            nbytes = int(ctx.lib.pcs_map_inbox_bytes(self.capacity, self.world))
+            for b in range(2):
+                self._inbox[b] = ctx.dev_alloc(nbytes)
+                ctx.memset(self._inbox[b], 0, 256)
+            ctx.sync()
+            mine_h = torch.tensor(list(ctx.ipc_export(self._inbox[0]) + ctx.ipc_export(self._inbox[1])), dtype=torch.uint8,
+                                  device=self.device)
+            all_h = torch.empty(self.world * 128, dtype=torch.uint8, device=self.device)
+            dist.all_gather_into_tensor(all_h, mine_h)
+            all_h = all_h.cpu().numpy().tobytes()
+            for b in range(2):
+                for r in range(self.world):
+                    self._peer_inbox[b].append(0 if r == self.rank else ctx.ipc_open(all_h[128 * r + 64 * b: 128 * r + 64 * (b + 1)]))
         self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._epoch = 0
         self.owned_map = self._mine[0]
@@ -286,12 +312,19 @@ class PeerMapExchange:
             mark("clear_owned")
         src = self.local if local is None else local
         # the maps are plain device tables: every call below runs on THIS exchange's context (stream), whoever made them
-        _push(self.ctx, src, self._owners[b], self.clear_local)
+        if self.mode == "mailbox":
+            self.ctx.push_mailbox(src, self._mine[b], self.rank, self._peer_inbox[b], self.capacity, self.clear_local)
+        else:
+            _push(self.ctx, src, self._owners[b], self.clear_local)
         if mark:
             mark("push")
         self._barrier()                                # all pushes into parity b have landed everywhere
         if mark:
             mark("barrier")
+        if self.mode == "mailbox":
+            self.ctx.merge_inbox(self._mine[b], self._inbox[b], self.rank, self.world, self.capacity)
+            if mark:
+                mark("merge")
         self.owned_map = self._mine[b]
         self._epoch += 1
 
@@ -303,6 +336,15 @@ class PeerMapExchange:
                 if r != self.rank:
                     m.destroy()
         self._owners = [[], []]
+        for b in range(2):
+            for p in self._peer_inbox[b]:
+                if p:
+                    self.ctx.ipc_close(p)
+        self._peer_inbox = [[], []]
         self.dist.barrier()
+        for b in range(2):
+            if self._inbox[b]:
+                self.ctx.dev_free(self._inbox[b])
+                self._inbox[b] = None
         for m in self._mine:
             m.destroy()

@@ -46,7 +46,13 @@ def main():
     nccl.allgather_owned(GpuMapAdapter(ctx, full))
     kf, af, bf, _ = full.export()
 
-    peer = PeerMapExchange(ctx, local, dist, torch, cap)
+    at = PeerMapExchange(ctx, local, dist, torch, cap, mode="atomics", barrier="flags")  # remote atomics, stream-memop barrier
+    at.exchange()
+    at.exchange()
+    ctx.sync()
+    k3, a3, b3, _ = at.owned_map.export()
+    at.close()
+    peer = PeerMapExchange(ctx, local, dist, torch, cap)  # mailbox records, kernel barrier (defaults)
     peer.exchange()
     peer.exchange()
     ctx.sync()
@@ -80,7 +86,7 @@ def main():
         ctx.d2h(of, d_of)
         emitted = dict(ov=ov, of=of)
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), k1=k1, a1=a1, b1=b1, k2=k2, a2=a2, b2=b2, kf=kf, af=af, bf=bf,
-             mesh_flags=mesh_flags, **emitted)
+             k3=k3, a3=a3, b3=b3, mesh_flags=mesh_flags, **emitted)
     peer.close()
     dist.barrier()
     dist.destroy_process_group()

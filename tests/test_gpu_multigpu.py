@@ -42,7 +42,7 @@ def test_exchange_world2_nccl_and_peer_memory(ctx, pcs, tmp_path):
     outs = [np.load(os.path.join(tmp_path, f"rank{r}.npz")) for r in range(world)]
     for r, o in enumerate(outs):
         mine = np.array([pcs.capi.mix64(int(k)) % world == r for k in keys])
-        for tag in ("1", "2"):  # NCCL records, peer memory
+        for tag in ("1", "2", "3"):  # NCCL records, peer memory with mailboxes, peer memory with remote atomics
             assert np.array_equal(o["k" + tag], keys[mine]), (r, tag)
             assert np.array_equal(o["a" + tag], c0[mine]) and np.array_equal(o["b" + tag], c1[mine]), (r, tag)
         assert np.array_equal(o["kf"], keys) and np.array_equal(o["af"], c0) and np.array_equal(o["bf"], c1)
