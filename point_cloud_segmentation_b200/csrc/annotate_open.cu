@@ -5,17 +5,23 @@
 // pcs_detection/src_python/pcs_detection/models/histogram_backprojection.py:40-41, cv2.morphologyEx on a {0,255} mask).
 // An opened mask pixel depends on the 9x9 neighbourhood of thresholded pixels, so the kernel works on the organized grid:
 //
-//   * a CTA owns a band of 256 columns and a section of rows of one frame and marches down the rows, 4 rows (a chunk) at a
-//     time; each row segment (256 + 4 + 4 halo points, 8.25 KiB contiguous) is brought into a shared-memory ring by one
-//     TMA bulk copy (cp.async.bulk ... mbarrier::complete_tx) issued by one thread, one chunk ahead of its use, so no
-//     registers are spent on staging and every point is read from HBM once (+ halo: 4 rows per section end, 4 columns per
-//     band side; no BGR plane, no mask image, no second pass over the cloud);
-//   * the threshold result of a chunk is bit-packed with warp ballots (32 pixels per word, 10 words per row incl. halo);
-//   * the opening is separable and runs on the packed words: a 5-wide min is 4 shifts + 4 ANDs of a 64-bit window, a
-//     5-tall min is 4 ANDs of rows held by neighbouring lanes (shuffles), dilation likewise with ORs; each warp does this
-//     for its own 32 columns, so there is no second block-wide barrier;
+//   * a CTA owns a band of 256 columns and a section of ~180 rows of one frame and marches down the rows, 4 rows (a chunk)
+//     at a time.  A PRODUCER warp brings each row segment (256 + 4 + 4 halo points, 8.25 KiB contiguous) into a 12-row
+//     shared-memory ring with one TMA bulk copy (cp.async.bulk ... mbarrier::complete_tx, L2::evict_first), chunk after
+//     chunk, as soon as the consumers have released the ring chunk (`empty` mbarriers); no registers are spent on staging
+//     and every point is read from HBM once (+ halo: 4 rows per section end, 4 columns per band side; no BGR plane, no mask
+//     image, no second pass over the cloud);
+//   * 16 CONSUMER warps (two groups of 8, each group takes 2 of the 4 rows of a chunk) wait on the chunk's `full` mbarrier,
+//     threshold their rows with host-built decision tables (hsv.cuh) and bit-pack the result with warp ballots (32 pixels per
+//     word).  A word column (32 columns) thresholds its 4 + 4 neighbouring pixels again instead of fetching them from the
+//     neighbouring warps, so the word columns run independently of each other: there is no block-wide barrier per chunk,
+//     only a named barrier between the two warps of a column;
+//   * the opening is separable and runs on the packed words: a 5-wide min is 3 shift/AND steps on a 64-bit window, a 5-tall
+//     min is 4 ANDs of rows held by neighbouring lanes (shuffles), dilation likewise with ORs; group 0's warp does it for
+//     the column and publishes the opened rows (the instruction count of this step does not depend on the lanes in use);
 //   * four rows behind the threshold front the mask is final and the points -- still in the ring -- are finished exactly as
-//     in annotate.cu (label, transform, annotated cloud + mask stores, warp-aggregated voxel update).
+//     in annotate.cu (label, transform, annotated cloud + mask stores, warp-aggregated voxel update; the table lookups of a
+//     thread's rows are issued back to back).
 //
 // Border rule of cv2 (BORDER_CONSTANT with morphologyDefaultBorderValue): pixels outside the image do not take part in
 // either the erosion or the dilation = thresholded pixels outside the image count as 1, eroded pixels outside as 0.
