@@ -105,6 +105,46 @@ def test_full_size_properties(ctx, pcs, O, n_frames, w, h, res, cap):
     scan.free()
 
 
+def test_full_size_scan_with_the_opening(ctx, pcs, O):
+    """configs[1] at full size through annotate_open_kernel (one launch for 300 frames, bands x sections x frames CTAs):
+    label counts agree with the mask, the un-opened run dominates it pixel-wise (an opening only removes), and sampled
+    frames -- first, middle, last: every frame boundary case of the grid decode -- equal the oracle byte for byte."""
+    n_frames, w, h, res, cap = 300, 1280, 720, 0.005, 1 << 21
+    scan = Scan(ctx, pcs, n_frames, w, h)
+    n_pts = n_frames * scan.ppf
+    d_ann, d_mask = ctx.dev_alloc(n_pts * 32), ctx.dev_alloc(n_pts)
+    vmap = ctx.create_map(res, cap)
+    p_open = pcs.annotate_params(pcs.hsv_params(morph_open=1), lower=255, upper=255)
+    ctx.annotate_frames_dev(scan.d_in, n_frames, w, h, scan.d_pose, p_open, vmap, d_ann, d_mask)
+    keys, c0, c1, _ = vmap.export()
+    mask = np.empty(n_pts, np.uint8)
+    ctx.d2h(mask, d_mask)
+    xs = np.empty(n_pts * 8, np.float32)
+    ctx.d2h(xs, scan.d_in)
+    fin = np.isfinite(xs[0::8])
+    del xs
+    assert set(np.unique(mask).tolist()) <= {0, 255}
+    assert int(c1.sum(dtype=np.uint64)) == int(((mask == 255) & fin).sum())
+    assert int(c0.sum(dtype=np.uint64)) + int(c1.sum(dtype=np.uint64)) == int(fin.sum())
+    plain = np.empty(n_pts, np.uint8)
+    ctx.annotate_frames_dev(scan.d_in, n_frames, w, h, scan.d_pose, pcs.annotate_params(lower=255, upper=255), None, None, d_mask)
+    ctx.d2h(plain, d_mask)
+    assert not ((mask == 255) & (plain == 0)).any() and int((plain == 255).sum()) > int((mask == 255).sum()) > 0
+    op = O.default_params(morph_open=1)
+    for f in (0, 1, n_frames // 2, n_frames - 1):
+        o_ann, o_mask = O.annotate_frame(scan.frame(pcs, f), w, h, op)
+        assert np.array_equal(mask[f * scan.ppf:(f + 1) * scan.ppf].reshape(h, w), o_mask), f
+        assert scan.frame(pcs, f, d_ann).tobytes() == o_ann.tobytes(), f
+    # map-only variant of the kernel: same map
+    vmap.clear()
+    ctx.annotate_frames_dev(scan.d_in, n_frames, w, h, scan.d_pose, p_open, vmap, None, None)
+    assert all(np.array_equal(x, y) for x, y in zip(vmap.export()[:3], (keys, c0, c1)))
+    vmap.destroy()
+    ctx.dev_free(d_ann)
+    ctx.dev_free(d_mask)
+    scan.free()
+
+
 def test_mesh_mask_2m_triangles_properties(ctx, pcs, O):
     """configs[3]-shaped: 2 M-triangle height-field against an aggregated 5 mm map; INSIDE + OUTSIDE partition the mesh,
     flags agree with the oracle on a sampled sub-mesh."""
