@@ -537,11 +537,10 @@ def main():
             "clocks": clocks.summary(),
             "map": {"voxels": n_vox, "occupied": n_occ, "which": "owned slice of the exchanged map" if world > 1 else "whole map"},
         }
-        if exch is not None and exch.kind == "peer":
-            line["config"]["exchange_barrier"] = exch.barrier_kind
-            line["config"]["exchange_mode"] = getattr(exch.exch, "mode", None)
-            line["config"]["exchange_overlap"] = ("exchange of scan k on a side stream while the kernel of scan k+1 runs "
-                                                  "(two local maps)") if exch.pipelined else "in line after every kernel"
+        if exch is not None:  # how the exchange ran (kept out of `config`, which both arms print identically)
+            line["exchange"] = {"kind": exch.kind, "mode": getattr(exch.exch, "mode", None), "barrier": exch.barrier_kind,
+                                "overlap": ("exchange of scan k on a side stream while the kernel of scan k+1 runs (two "
+                                            "local maps)") if exch.pipelined else "in line after every kernel"}
         for k, v in (("exchange_check", exchange_check), ("mesh_mask", mesh), ("detector", detector), ("config1", config1),
                      ("config5", config5)):
             if v is not None:
