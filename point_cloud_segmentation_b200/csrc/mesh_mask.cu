@@ -317,7 +317,7 @@ __device__ __forceinline__ void box_from_records(unsigned long long r0, unsigned
 //   * no such vertex, and the key box consists of the vertex voxels only  -> no contact (those voxels are known to be empty;
 //     this is the usual case for a mesh finer than the voxels)
 //   * anything else (other voxels to probe, unusable record)              -> to-do list of mesh_undecided_kernel, appended
-//     with one atomic per CTA; the flag is written 0 here and overwritten there on contact.
+//     with one atomic per warp that has any; the flag is written 0 here and overwritten there on contact.
 // The kernel makes no calls and holds no coordinates, so it stays small in registers and code.
 __global__ void __launch_bounds__(256, 4) mesh_tri_kernel(const double* __restrict__ verts, unsigned long long nv,
                                                          const int* __restrict__ faces4, unsigned long long nt,
@@ -325,9 +325,8 @@ __global__ void __launch_bounds__(256, 4) mesh_tri_kernel(const double* __restri
                                                          uint8_t* __restrict__ flags, unsigned int* __restrict__ todo,
                                                          unsigned int* __restrict__ todo_count)
 {
-  __shared__ unsigned int s_warp_count[8], s_base;
   launch_dependents();
-  const unsigned int lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  const unsigned int lane = threadIdx.x & 31u;
   const unsigned long long t0 = (unsigned long long)blockIdx.x * (blockDim.x * kTriPerThread) + threadIdx.x;
   int4 f[kTriPerThread];
 #pragma unroll
@@ -375,7 +374,7 @@ __global__ void __launch_bounds__(256, 4) mesh_tri_kernel(const double* __restri
     if (t < nt)
       flags[t] = hit ? 1 : 0;
   }
-  // one to-do slot range per CTA
+  // one to-do slot range per warp (a warp with nothing undecided, the usual case, issues no atomic and meets no barrier)
   const unsigned int mine = (unsigned int)__popc(und_mask);
   unsigned int incl = mine;
 #pragma unroll
@@ -385,23 +384,14 @@ __global__ void __launch_bounds__(256, 4) mesh_tri_kernel(const double* __restri
     if (lane >= (unsigned int)o)
       incl += v;
   }
-  if (lane == 31)
-    s_warp_count[warp] = incl;
-  __syncthreads();
-  if (threadIdx.x == 0)
-  {
-    unsigned int total = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++)
-    {
-      const unsigned int c = s_warp_count[w];
-      s_warp_count[w] = total;
-      total += c;
-    }
-    s_base = total ? atomicAdd(todo_count, total) : 0u;
-  }
-  __syncthreads();
-  unsigned int dst = s_base + s_warp_count[warp] + incl - mine;
+  const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
+  if (total == 0)
+    return;
+  unsigned int base = 0;
+  if (lane == 0)
+    base = atomicAdd(todo_count, total);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  unsigned int dst = base + incl - mine;
 #pragma unroll
   for (int j = 0; j < kTriPerThread; j++)
     if (und_mask & (1u << j))
