@@ -133,11 +133,10 @@ inline size_t compact_scratch_bytes(unsigned long long n)
   return ((nb * sizeof(unsigned int) + 15) & ~(size_t)15) + (nb + 1) * sizeof(unsigned long long);
 }
 
-// Enqueues the three launches.  `scratch` must hold compact_scratch_bytes(n).  The total lands at offsets[n_blocks];
-// its device address is returned through d_total.
-template <class Pred, class Emit>
-int compact_run(pcs_ctx* ctx, Pred pred, Emit emit, unsigned long long n, void* scratch,
-                const unsigned long long** d_total)
+// Count + scan only: per-block exclusive offsets for a caller that brings its own scatter kernel (same block shape:
+// kCompactThreads threads, kCompactRounds rounds, item = base + round * kCompactThreads + thread).
+template <class Pred>
+int compact_offsets(pcs_ctx* ctx, Pred pred, unsigned long long n, void* scratch, unsigned long long** offsets_out)
 {
   const unsigned int nb = compact_blocks(n);
   unsigned int* counts = reinterpret_cast<unsigned int*>(scratch);
@@ -150,6 +149,19 @@ int compact_run(pcs_ctx* ctx, Pred pred, Emit emit, unsigned long long n, void* 
   }
   compact_scan_kernel<<<1, 1024, 0, ctx->stream>>>(counts, offsets, nb);
   count_launch(ctx);
+  *offsets_out = offsets;
+  return check_launch("compact_offsets");
+}
+
+// Enqueues the three launches.  `scratch` must hold compact_scratch_bytes(n).  The total lands at offsets[n_blocks];
+// its device address is returned through d_total.
+template <class Pred, class Emit>
+int compact_run(pcs_ctx* ctx, Pred pred, Emit emit, unsigned long long n, void* scratch,
+                const unsigned long long** d_total)
+{
+  const unsigned int nb = compact_blocks(n);
+  unsigned long long* offsets = nullptr;
+  PCS_TRY(compact_offsets(ctx, pred, n, scratch, &offsets));
   if (nb > 0)
   {
     compact_scatter_kernel<<<nb, kCompactThreads, 0, ctx->stream>>>(pred, emit, n, offsets);

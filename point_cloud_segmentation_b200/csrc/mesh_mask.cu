@@ -617,6 +617,64 @@ struct TriEmit
   }
 };
 
+// Scatter of the kept triangles with coalesced stores.  The generic compact_scatter_kernel would have every kept thread
+// write its own 72 + 16 + 9 bytes (8-byte pieces 72 bytes apart across the warp).  Here the kept lanes of a warp -- whose
+// outputs are contiguous, the compaction being order preserving -- first lay their nine coordinates down in shared memory
+// in output order; the whole warp then streams that run out with consecutive 8-byte words per lane, likewise the colour
+// bytes; the 16-byte faces are contiguous per kept lane already.
+__global__ void __launch_bounds__(kCompactThreads) tri_emit_scatter_kernel(FlagPred pred, TriEmit emit, unsigned long long n,
+                                                                          const unsigned long long* __restrict__ offsets)
+{
+  __shared__ unsigned int s_warp[kCompactThreads / 32];
+  __shared__ double s_v[kCompactThreads / 32][32 * 9];
+  const unsigned long long base = (unsigned long long)blockIdx.x * kCompactItems;
+  unsigned long long running = offsets[blockIdx.x];
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int r = 0; r < kCompactRounds; r++)
+  {
+    const unsigned long long t = base + (unsigned long long)r * kCompactThreads + threadIdx.x;
+    const bool keep = (t < n) && pred(t);
+    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0)
+      s_warp[warp] = __popc(ballot);
+    __syncthreads();
+    unsigned int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kCompactThreads / 32; w++)
+    {
+      const unsigned int c = s_warp[w];
+      before += (w < (int)warp) ? c : 0u;
+      total += c;
+    }
+    const unsigned int k = __popc(ballot), rank = __popc(ballot & ((1u << lane) - 1u));
+    const unsigned long long first = running + before;  // output index of this warp's first kept triangle
+    // room left in the caller's buffers (emit.cap triangles): the count is still exact, the excess is not written
+    const unsigned int room = first >= emit.cap ? 0u : (unsigned int)(emit.cap - first < k ? emit.cap - first : k);
+    if (keep && rank < room)
+    {
+      const int4 f = reinterpret_cast<const int4*>(emit.faces4)[t];
+      const int idx[3] = { f.y, f.z, f.w };
+#pragma unroll
+      for (int j = 0; j < 3; j++)
+#pragma unroll
+        for (int ax = 0; ax < 3; ax++)
+          s_v[warp][rank * 9 + 3 * j + ax] = emit.verts[3ull * idx[j] + ax];
+      const unsigned long long dst = first + rank;
+      reinterpret_cast<int4*>(emit.out_faces4)[dst] = make_int4(3, (int)(3 * dst), (int)(3 * dst + 1), (int)(3 * dst + 2));
+    }
+    __syncwarp();
+    double* ov = emit.out_verts + 9ull * first;
+    uint8_t* orgb = emit.out_rgb + 9ull * first;
+    for (unsigned int i = lane; i < 9u * room; i += 32)
+    {
+      ov[i] = s_v[warp][i];
+      orgb[i] = (i % 3u == 1u) ? 128 : 0;  // octomap_mesh_masking.cpp:224,278: all (0,128,0)
+    }
+    running += total;
+    __syncthreads();
+  }
+}
+
 struct NullEmit
 {
   __device__ void operator()(unsigned long long, unsigned long long) const {}
@@ -755,7 +813,13 @@ static int mesh_assemble_dev(pcs_ctx* ctx, const double* d_verts, uint64_t nv, c
   if (d_ov && d_of && d_orgb)
   {
     TriEmit emit{ d_verts, d_faces, d_ov, d_of, d_orgb, cap };
-    PCS_TRY(compact_run(ctx, pred, emit, nt, scr, d_total_out));
+    unsigned long long* offsets = nullptr;
+    PCS_TRY(compact_offsets(ctx, pred, nt, scr, &offsets));
+    const unsigned int nb = compact_blocks(nt);
+    tri_emit_scatter_kernel<<<nb, kCompactThreads, 0, ctx->stream>>>(pred, emit, nt, offsets);
+    count_launch(ctx);
+    PCS_TRY(check_launch("tri_emit_scatter_kernel"));
+    *d_total_out = offsets + nb;
   }
   else
     PCS_TRY(compact_run(ctx, pred, NullEmit{}, nt, scr, d_total_out));
